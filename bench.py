@@ -1,0 +1,382 @@
+#!/usr/bin/env python
+"""bench.py -- the hot path (SparseMatrix::AddMatMat on the GPU) on BASELINE.json's configs.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg2] [--impl ours|reference]
+
+A step = one pass of the product over one batch of synthetic input:
+  cfg1  SpMV  4096 x 4096, 1 % dense, m = 1
+  cfg2  SpMM  4096 x 4096, 90 % sparse, x dense 4096 x 128           (default; BASELINE.json configs[1])
+  cfg3  SpMM  16384 x 16384, 95 % sparse, x dense N = 512
+  cfg4  SpMV  power-law rows (Pareto, ~16 nnz/row), 2^23 rows, direct CSR
+alpha = beta = 1 (the reference's own sparse benchmark setting, src/test/blas_test.h:313).
+
+N > 1 (torchrun, one rank per GPU): weak scaling over row slabs -- rank r holds its own
+slab of W (the rows r*n .. (r+1)*n of a matrix N times as tall), X is replicated, each
+rank produces its Y slab; no collective on the data path.  `value` = work of all ranks /
+max-over-ranks device time.
+
+One JSON line on stdout (rank 0).  See the task contract for the keys; additions here:
+roofline (dominant kernel, event-timed through sblas_b200_profile_*), cpu_baseline
+(the unmodified reference, oracle/_ref, on the host cores), e2e (host buffers through the
+reference-facing host entry point, copies inside the timed region).
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from sparsematrix_b200 import gen  # noqa: E402
+
+WORKLOADS = {
+    #        kind    n      k      density  m    seed
+    "cfg1": ("spmv", 4096, 4096, 0.01, 1, 11),
+    "cfg2": ("spmm", 4096, 4096, 0.10, 128, 12),
+    "cfg3": ("spmm", 16384, 16384, 0.05, 512, 13),
+    "cfg4": ("spmv_powerlaw", 1 << 23, 1 << 23, None, 1, 14),
+}
+DESCR = {
+    "cfg1": "SpMV random 4096x4096 1% density (BASELINE.json configs[0])",
+    "cfg2": "pruned-weight SpMM 4096x4096 at 90% sparsity x dense 4096x128 (BASELINE.json configs[1])",
+    "cfg3": "SpMM 16384x16384 at 95% sparsity x dense N=512 (BASELINE.json configs[2])",
+    "cfg4": "power-law SpMV 2^23 rows ~16 nnz/row, direct CSR (BASELINE.json configs[3])",
+}
+FP32_PEAK_TFLOPS = 2 * 128 * 148 * 1.965e9 / 1e12     # CUDA-core FMA peak at max clock
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def build_inputs(workload, rank, scale_rows=1.0):
+    """Host-side inputs of one rank: the matrix (codes or CSR), A (m x k), C (m x n)."""
+    kind, n, k, dens, m, seed = WORKLOADS[workload]
+    n = int(n * scale_rows)
+    tab = gen.codebook(255, 1)
+    a = gen.dense_uniform((m, k), 2)                       # X is replicated: same on every rank
+    c = np.zeros((m, n), np.float32)                       # C = 0 for timing
+    if kind == "spmv_powerlaw":
+        row_ptr, col, code = gen.powerlaw_csr(n, k, seed + 1000 * rank)
+        return dict(kind=kind, n=n, k=k, m=m, tab=tab, a=a, c=c, csr=(row_ptr, col, code), nnz=int(row_ptr[-1]))
+    codes = gen.codes_bernoulli(n, k, dens, seed + 1000 * rank)
+    return dict(kind=kind, n=n, k=k, m=m, tab=tab, a=a, c=c, codes=codes, nnz=int((codes != 255).sum()))
+
+
+def algorithmic_bytes(inp):
+    """Bytes the dominant kernel must move once: 4 B column + 1 B code per non-zero,
+    row_ptr, X once, C read + written (beta = 1)."""
+    n, k, m, nnz = inp["n"], inp["k"], inp["m"], inp["nnz"]
+    return 5 * nnz + 4 * (n + 1) + 4 * k * m + 8 * n * m
+
+
+class ClockSampler:
+    """SM clock + throttle reasons of one GPU while the timed region runs (pynvml, ~2 ms period)."""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz, self._stop, self._t = [], set(), None, False, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self._stop:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.002)
+
+    def __enter__(self):
+        if self.nv:
+            self._t = threading.Thread(target=self._run, daemon=True)
+            self._t.start()
+        return self
+
+    def __exit__(self, *exc):
+        self._stop = True
+        if self._t:
+            self._t.join()
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": 0}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+class CpuReference:
+    """The reference's own CPU implementation of the step on this rank's inputs: the unmodified
+    library (oracle/_ref, kind "reference") when it was built, else the C port (kind "port").
+    The 2^23-row power-law shape cannot be held by the reference's format at all:
+    there the CSR restatement runs on a bounded sample (the first 2^20 rows) and is scaled by nnz."""
+
+    def __init__(self, inp):
+        from oracle import oracle as O      # bench.py's only use of oracle/: the CPU baseline legs
+        self.inp, self.scale = inp, 1.0
+        a, m, n, k = inp["a"], inp["m"], inp["n"], inp["k"]
+        if inp["kind"] == "spmv_powerlaw":
+            row_ptr, col, code = inp["csr"]
+            rows = min(n, 1 << 20)
+            rp = np.ascontiguousarray(row_ptr[: rows + 1])
+            self.scale = inp["nnz"] / float(rp[-1])
+            self.kind, self.rows = "port", rows
+            self.sample = f"first {rows} rows of the same matrix ({1 / self.scale:.3f} of the nnz), time scaled by nnz"
+            self._run = lambda c: O.addmatmat_csr(rp, col, code, inp["tab"], 255, rows, k, a, 1, k, c, rows, 1.0, 1.0)
+            return
+        self.rows = n
+        self.sample = "full workload, one AddMatMat call per step"
+        if O.have_ref():
+            R = O.RefMatrix()
+            R.CopyForm(inp["codes"], n, k, k, inp["tab"], 255, True)
+            self.kind, self._keep = "reference", R
+            self._run = lambda c: R.AddMatMat(a, m, k, c, n, 1.0, 1.0)
+        else:
+            st = O.copyform(inp["codes"], n, k, k, inp["tab"], 255, True)
+            self.kind = "port"
+            self._run = lambda c: O.addmatmat(st, a, m, k, c, n, 1.0, 1.0)
+
+    def call(self):
+        """One step; seconds for the whole workload."""
+        c = np.ascontiguousarray(self.inp["c"][:, : self.rows])
+        c = c.copy()
+        t0 = time.perf_counter()
+        self._run(c)
+        return (time.perf_counter() - t0) * self.scale
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+METRIC = "SpMV/SpMM GFLOP/s (2*nnz*m / time)"
+
+
+def config_of(args, inp, extra=None):
+    cfg = {"workload": args.workload, "descr": DESCR[args.workload], "n_per_gpu": inp["n"], "k": inp["k"],
+           "m": inp["m"], "nnz_per_gpu": inp["nnz"], "alpha": 1.0, "beta": 1.0}
+    cfg.update(extra or {})
+    return cfg
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the same step on the host cores.
+    The library is single-threaded, so "all the host threads it can use" is 1."""
+    rank, _, _ = dist_env()
+    if rank != 0:
+        return
+    inp = build_inputs(args.workload, 0, args.scale_rows)
+    flops = 2.0 * inp["nnz"] * inp["m"]
+    ref = CpuReference(inp)
+    first = ref.call()                                             # also the first warm-up step
+    # bound the run: at most ~90 s of CPU work in total
+    budget = max(1, int(90.0 / max(first / ref.scale, 1e-6)))
+    warm = max(0, min(args.warmup - 1, budget // 4))
+    steps = max(1, min(args.steps, budget - warm))
+    for _ in range(warm):
+        ref.call()
+    t0 = time.perf_counter()
+    times = [ref.call() for _ in range(steps)]
+    wall = time.perf_counter() - t0
+    sec = float(np.mean(times))
+    val = flops / sec / 1e9
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "GFLOP/s", "n_gpus": args.gpus, "steps": steps,
+        "warmup": warm + 1, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config_of(args, inp),
+        "cpu_baseline": {"value": val, "unit": "GFLOP/s", "cores": 1, "kind": ref.kind, "sample": ref.sample},
+        "e2e": {"value": val, "unit": "GFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "wall_s": wall,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import sparsematrix_b200 as sb
+
+    rank, local_rank, world = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this library has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dev = torch.device("cuda", local_rank)
+
+    inp = build_inputs(args.workload, rank, args.scale_rows)
+    n, k, m, nnz = inp["n"], inp["k"], inp["m"], inp["nnz"]
+    if inp["kind"] == "spmv_powerlaw":
+        row_ptr, col, code = inp["csr"]
+        mat = sb.DeviceMatrix.upload_csr(row_ptr, col, code, inp["tab"], 255, n, k, device=local_rank)
+        host_obj = None
+    else:
+        host_obj = sb.SparseMatrix(inp["codes"], n, k, k, inp["tab"], 255, sb.SparseMatrix.Trans)
+        mat = host_obj.device_matrix()                      # upload (once); borrowed handle
+    info = mat.info()
+    assert info.nnz == nnz, (info.nnz, nnz)
+    flops = 2.0 * nnz * m
+    bytes_alg = algorithmic_bytes(inp)
+
+    d_a = torch.from_numpy(inp["a"]).to(dev)
+    d_c = torch.zeros((m, n), dtype=torch.float32, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)       # > 126 MB L2
+    stream = torch.cuda.current_stream()
+    L = sb.lib()
+
+    def step_dev():
+        mat.addmatmat_dev(d_a, m, k, d_c, n, 1.0, 1.0, stream=stream.cuda_stream)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed_pass(steps, profile=False):
+        """K steps, L2 flushed before each, one event pair per step on the launching stream."""
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        if profile:
+            mat.profile_begin()
+        barrier()
+        for a_ev, b_ev in evs:
+            flush.zero_()
+            a_ev.record(stream)
+            step_dev()
+            b_ev.record(stream)
+        barrier()
+        ms = sum(a_ev.elapsed_time(b_ev) for a_ev, b_ev in evs)
+        if profile:
+            k_ms, k_cnt = mat.profile_end()
+            return ms, k_ms, k_cnt
+        return ms
+
+    for _ in range(max(args.warmup, 3)):
+        flush.zero_()
+        step_dev()
+    torch.cuda.synchronize()
+
+    launches0 = L.sblas_b200_launch_count()
+    with ClockSampler(local_rank) as clocks:
+        total_ms = timed_pass(args.steps)
+    launches = L.sblas_b200_launch_count() - launches0
+    # warm (L2-resident) variant, reported beside the cold number
+    barrier()
+    w0, w1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    w0.record(stream)
+    for _ in range(args.steps):
+        step_dev()
+    w1.record(stream)
+    barrier()
+    warm_ms = w0.elapsed_time(w1)
+    # dominant kernel alone (cold), for the roofline
+    _, kern_ms, kern_cnt = timed_pass(args.steps, profile=True)
+
+    # end to end through the reference-facing host entry point: pinned host buffers,
+    # H2D of A and C, kernels, D2H of C inside every timed step
+    h_a = torch.from_numpy(inp["a"]).pin_memory()
+    h_c = torch.zeros((m, n), dtype=torch.float32).pin_memory()
+    e2e_steps = max(3, min(args.steps, 50))
+    for _ in range(3):
+        mat.addmatmat_host(h_a, m, k, h_c, n, 1.0, 1.0)
+    barrier()
+    e2e_s = 0.0
+    for _ in range(e2e_steps):
+        flush.zero_()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        mat.addmatmat_host(h_a, m, k, h_c, n, 1.0, 1.0)      # returns when h_c is valid
+        e2e_s += time.perf_counter() - t0
+    checksum = float(h_c.sum())
+
+    t = torch.tensor([total_ms, warm_ms, e2e_s * 1e3, kern_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms, warm_ms, e2e_ms, kern_ms_max = [float(x) for x in t.tolist()]
+
+    if rank == 0:
+        hbm_peak, peak_src = measured_peaks()
+        ms_step = total_ms / args.steps
+        value = world * flops / (ms_step * 1e-3) / 1e9
+        kern_us = kern_ms / max(kern_cnt, 1) * 1e3
+        ach = bytes_alg / (kern_us * 1e-6) / 1e9
+        t_roof_us = max(bytes_alg / (hbm_peak * 1e9), flops / (FP32_PEAK_TFLOPS * 1e12)) * 1e6
+        line = {
+            "metric": METRIC, "value": value, "unit": "GFLOP/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": config_of(args, inp, {
+                "l2": "flushed before every timed step (256 MiB write); per-step CUDA events summed",
+                "sharding": "row slabs of W, X replicated, no data-path collective" if world > 1 else "single GPU",
+                "device_format": "CSR(W=S^T) int32 col + u8 code, 5 B/nnz", "spmv_lanes": info.spmv_lanes,
+                "long_rows": info.long_rows}),
+            "effective_gbs": world * bytes_alg / (ms_step * 1e-3) / 1e9,
+            "warm_l2": {"ms_per_step": warm_ms / args.steps, "value": world * flops / (warm_ms / args.steps * 1e-3) / 1e9},
+            "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
+                         "traffic": None, "peak_source": peak_src, "kernel_us": kern_us,
+                         "algorithmic_bytes": bytes_alg, "algorithmic_flops": flops,
+                         "fp32_frac": flops / (kern_us * 1e-6) / (FP32_PEAK_TFLOPS * 1e12),
+                         "t_roof_us": t_roof_us, "roof_frac": t_roof_us / kern_us,
+                         "kernel_share_of_step": kern_us / (ms_step * 1e3)},
+            "e2e": {"value": world * flops / (e2e_ms / e2e_steps * 1e-3) / 1e9, "unit": "GFLOP/s",
+                    "h2d_bytes_per_step": int(4 * m * (k + n)), "d2h_bytes_per_step": int(4 * m * n),
+                    "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps,
+                    "api": "sblas_b200_addmatmat_host (pinned host A, C; synchronous)", "checksum": checksum},
+            "gpu_launches": int(launches), "clocks": clocks.summary(),
+        }
+        if args.cpu_baseline and world >= 1:
+            ref = CpuReference(inp)
+            ref.call()
+            reps = 3 if ref.call() < 5 else 1
+            best = min(ref.call() for _ in range(reps))
+            line["cpu_baseline"] = {"value": flops / best / 1e9, "unit": "GFLOP/s", "cores": 1, "kind": ref.kind,
+                                    "sample": ref.sample + f"; best of {reps}", "ms_per_step": best * 1e3,
+                                    "host_cores_available": os.cpu_count()}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--workload", choices=sorted(WORKLOADS), default="cfg2")
+    ap.add_argument("--scale-rows", type=float, default=1.0, help="shrink n for quick checks (not a bench value)")
+    ap.add_argument("--no-cpu-baseline", dest="cpu_baseline", action="store_false")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,177 @@
+/*
+ * sblas_b200.h -- C ABI of the B200 (sm_100a) implementation of the
+ * NeverLEX/sparsematrix sparse x dense product path.
+ *
+ * This is the drop-in boundary.  The reference computes
+ *      C[m x n] = beta*C + alpha * A[m x k] * S[k x n]
+ * in sblas::SparseMatrix<uint8,uint8,float>::AddMatMat
+ * (reference src/sparse/sparse-matrix.cc:139-194), which calls three free
+ * CPU kernels with raw pointers (src/sparse/kernel.h:42-62; call sites
+ * sparse-matrix.cc:150,181-189).  The entry points below are what that member
+ * function binds instead: the object's compressed members go to
+ * sblas_b200_upload() once, and each AddMatMat call becomes one
+ * sblas_b200_addmatmat_host() (same pointers, same meaning) or, for callers
+ * that keep activations on the device, sblas_b200_addmatmat_dev().
+ * INTEGRATION.md shows the reference-side patch.
+ *
+ * Plain C: pointers and sizes only, no C++/torch types, no exceptions.
+ * Every function returns an int status: SBLAS_B200_OK (0) or a negative
+ * SBLAS_B200_E* code; sblas_b200_last_error() gives the thread's last message.
+ * There is no CPU fallback: without a CUDA device every call that needs one
+ * fails with SBLAS_B200_ECUDA.
+ *
+ * Thread-safety (mirrors the reference): an uploaded matrix is
+ * immutable; concurrent products on one handle are serialised on the handle's
+ * workspace lock; upload/free of different handles are independent.
+ */
+#ifndef SBLAS_B200_H_
+#define SBLAS_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define SBLAS_B200_API __attribute__((visibility("default")))
+#else
+#define SBLAS_B200_API
+#endif
+
+#define SBLAS_B200_OK        0
+#define SBLAS_B200_EINVAL   -1   /* bad argument (null pointer, negative size, ld too small, ...) */
+#define SBLAS_B200_ECUDA    -2   /* a CUDA call failed, or no device */
+#define SBLAS_B200_ENOMEM   -3   /* host or device allocation failed */
+#define SBLAS_B200_EFORMAT  -4   /* the compressed stream / CSR is inconsistent */
+
+#define SBLAS_B200_ABI_VERSION 1
+
+/* Device-resident matrix W = S^T (n x k), immutable after upload.  Opaque. */
+typedef struct sblas_b200_matrix sblas_b200_matrix;
+
+/* What sblas_b200_get_info() reports. */
+typedef struct sblas_b200_info {
+    int32_t device;          /* CUDA ordinal the matrix lives on */
+    int32_t s_rows;          /* k : rows of S (= rows_, sparse-matrix.h:50) */
+    int32_t s_cols;          /* n : columns of S held by this handle (= cols_, or the slab width) */
+    int32_t col_begin;       /* first S column of the slab (0 for a whole matrix) */
+    int32_t table_size;      /* T : valid codebook entries */
+    int32_t max_row_nnz;     /* longest row of W */
+    int32_t long_rows;       /* rows handled by the split-row SpMV path */
+    int32_t spmv_lanes;      /* sub-warp width the row-length histogram selected for SpMV */
+    int64_t nnz;             /* stored non-zeros (fillers dropped) */
+    int64_t fillers;         /* filler entries met in the stream (sparse-matrix.cc:46-51) */
+    int64_t entries;         /* nnz + fillers for stream uploads, nnz for CSR uploads */
+    int64_t device_bytes;    /* bytes of HBM held by the handle (format + workspace) */
+    int64_t row_len_hist[33];/* [0] = empty rows, [b] = rows with 2^(b-1) <= nnz < 2^b */
+} sblas_b200_info;
+
+/* ---- library ------------------------------------------------------------ */
+SBLAS_B200_API int32_t sblas_b200_abi_version(void);
+SBLAS_B200_API const char *sblas_b200_last_error(void);
+SBLAS_B200_API int sblas_b200_device_count(int32_t *count);
+/* Kernels launched by this library in this process so far (bench.py's gpu_launches). */
+SBLAS_B200_API int64_t sblas_b200_launch_count(void);
+
+/* ---- format upload ------------------------------------------------------ */
+/*
+ * Upload the compressed members of a sblas::SparseMatrix<uint8,uint8,float>
+ * (reference src/sparse/sparse-matrix.h:45-52, built by CopyForm,
+ * sparse-matrix.cc:21-99) and convert them on the device to the layout the
+ * kernels read.  Host pointers.
+ *   pos_index, val_index : the two byte streams, `entries` bytes each
+ *   val_table            : valid_table_size (+1 trailing zero, ignored) floats
+ *   block_bounds         : nblocks pairs (row_off, col_off)  -- row_off must be 0 (block_row_shift 0)
+ *   block_index_bounds   : nblocks pairs [start, end) into the streams
+ *   rows, cols           : rows_ (k) and cols_ (n)
+ * valid_table_size == 0 / entries == 0 give an empty matrix (sparse-matrix.cc:26).
+ */
+SBLAS_B200_API int sblas_b200_upload(const uint8_t *pos_index, const uint8_t *val_index, int64_t entries,
+                                     const float *val_table, int32_t valid_table_size,
+                                     const int32_t *block_bounds, const int32_t *block_index_bounds,
+                                     int32_t nblocks, int32_t rows, int32_t cols,
+                                     int32_t device, sblas_b200_matrix **out);
+
+/*
+ * Same, but keep only the S columns [col_begin, col_end) -- one row slab of W
+ * for one GPU.  col_begin must be a multiple of 256 (panel aligned) so the
+ * streams split without re-encoding; col_end is a multiple of 256 or == cols.
+ * The product entry points then take `c` pointing at column col_begin.
+ */
+SBLAS_B200_API int sblas_b200_upload_slab(const uint8_t *pos_index, const uint8_t *val_index, int64_t entries,
+                                          const float *val_table, int32_t valid_table_size,
+                                          const int32_t *block_bounds, const int32_t *block_index_bounds,
+                                          int32_t nblocks, int32_t rows, int32_t cols,
+                                          int32_t col_begin, int32_t col_end,
+                                          int32_t device, sblas_b200_matrix **out);
+
+/*
+ * Direct CSR upload of W (n x k) for shapes the panel format cannot hold
+ * (e.g. 2^23 rows: SURVEY.md 0.6c).  row_ptr[n+1], col[nnz] ascending inside a
+ * row, code[nnz] < T indexing table[T].  Host pointers.
+ */
+SBLAS_B200_API int sblas_b200_upload_csr(const int32_t *row_ptr, const int32_t *col, const uint8_t *code,
+                                         const float *table, int32_t valid_table_size,
+                                         int32_t n, int32_t k, int32_t device, sblas_b200_matrix **out);
+
+/*
+ * nnz-balanced, panel-aligned split of the S columns into `parts` contiguous
+ * slabs: col_splits[parts+1], col_splits[0] = 0,
+ * col_splits[parts] = cols, interior values multiples of 256.  Pure host code.
+ */
+SBLAS_B200_API int sblas_b200_partition(const int32_t *block_bounds, const int32_t *block_index_bounds,
+                                        int32_t nblocks, int32_t cols, int32_t parts, int32_t *col_splits);
+
+SBLAS_B200_API int sblas_b200_free(sblas_b200_matrix *mat);
+SBLAS_B200_API int sblas_b200_get_info(const sblas_b200_matrix *mat, sblas_b200_info *info);
+
+/* ---- the product (replaces the body of AddMatMat, sparse-matrix.cc:139-194) ---- */
+/*
+ * C = beta*C + alpha*A*S with HOST pointers, the reference's own signature:
+ * a is m x k row-major with leading dimension lda, c is m x n row-major with
+ * leading dimension ldc, updated in place.  Copies a and c to the device, runs
+ * the kernels, copies c back, and returns when c is valid.  Semantics kept
+ * from the reference: beta == 1 skips the scale, beta == 0 still multiplies
+ * (NaN/Inf in C propagate), alpha == 0 only scales, S columns that hold no
+ * entry only get the scale.
+ */
+SBLAS_B200_API int sblas_b200_addmatmat_host(sblas_b200_matrix *mat, const float *a, int32_t m, int32_t lda,
+                                             float *c, int32_t ldc, float alpha, float beta);
+
+/*
+ * The same product on DEVICE pointers (on mat's device), enqueued on `stream`
+ * (a cudaStream_t; NULL = the default stream) and not synchronised.  This is
+ * the timed path.
+ */
+SBLAS_B200_API int sblas_b200_addmatmat_dev(sblas_b200_matrix *mat, const float *d_a, int32_t m, int32_t lda,
+                                            float *d_c, int32_t ldc, float alpha, float beta, void *stream);
+
+/* ---- kernel timing (bench.py's roofline leg) ------------------------------ */
+/*
+ * Between _begin and _end every product on this handle brackets its dominant
+ * kernel (the SpMV row kernel for m == 1, the SpMM kernel otherwise -- not the
+ * transpose or the split-row fix-ups) with a CUDA event pair on the launching
+ * stream.  _end synchronises those events and returns the summed kernel time
+ * and the number of bracketed launches.
+ */
+SBLAS_B200_API int sblas_b200_profile_begin(sblas_b200_matrix *mat);
+SBLAS_B200_API int sblas_b200_profile_end(sblas_b200_matrix *mat, double *total_ms, int64_t *launches);
+
+/* ---- structure read-back (parity tests) --------------------------------- */
+/*
+ * Decode on the device and copy to the host: the function of CopyTo
+ * (sparse-matrix.cc:101-137) for the columns this handle holds.
+ *   trans == 0 : dense is s_rows x stride, dense[r*stride + j] = S(r, col_begin + j)
+ *   trans == 1 : dense is s_cols x stride, dense[j*stride + r] = S(r, col_begin + j)
+ * The whole leading x stride area is cleared first, like the reference's memset.
+ */
+SBLAS_B200_API int sblas_b200_decode_dense(const sblas_b200_matrix *mat, float *dense, int32_t stride, int32_t trans);
+
+/* Copy the device CSR of W back: row_ptr[s_cols+1], col[nnz], code[nnz] (host pointers). */
+SBLAS_B200_API int sblas_b200_export_csr(const sblas_b200_matrix *mat, int32_t *row_ptr, int32_t *col, uint8_t *code);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SBLAS_B200_H_ */

@@ -1,0 +1,54 @@
+/*
+ * sblas_b200_host.h -- C handle API over the host-side class sblas::SparseMatrix
+ * <uint8,uint8,float> of this build (sparsematrix_b200/src/sparse/sparse-matrix.h,
+ * the mirror of reference src/sparse/sparse-matrix.h:25-53).
+ *
+ * For language bindings (ctypes, cgo, JNI ...) that want the reference's object
+ * interface -- CopyForm / CopyTo / AddMatMat / NumRows / NumCols / Destroy -- rather
+ * than the raw device entry points of sblas_b200.h.  One function per member
+ * function, same argument order and meaning.  AddMatMat runs on the GPU.
+ */
+#ifndef SBLAS_B200_HOST_H_
+#define SBLAS_B200_HOST_H_
+
+#include <stdint.h>
+
+#include "sblas_b200.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct sblas_host_matrix sblas_host_matrix;
+
+SBLAS_B200_API sblas_host_matrix *sblas_host_create(void);                 /* SparseMatrix()            sparse-matrix.h:28 */
+SBLAS_B200_API void sblas_host_free(sblas_host_matrix *h);                 /* ~SparseMatrix()           :32 */
+SBLAS_B200_API void sblas_host_destroy(sblas_host_matrix *h);              /* Destroy()                 :34 */
+/* CopyForm(density_matrix, rows, cols, stride, vals, val_table_size, trans)  :35 ; trans: 0 NoTrans, 1 Trans */
+SBLAS_B200_API int sblas_host_copyform(sblas_host_matrix *h, const uint8_t *density_matrix, int32_t rows, int32_t cols,
+                                       int32_t stride, const float *vals, int32_t val_table_size, int32_t trans);
+/* CopyTo(density_matrix, stride, trans)                                      :36 */
+SBLAS_B200_API void sblas_host_copyto(sblas_host_matrix *h, float *density_matrix, int32_t stride, int32_t trans);
+/* AddMatMat(a, m, lda, c, ldc, alpha, beta)                                  :37 ; returns the C-ABI status */
+SBLAS_B200_API int sblas_host_addmatmat(sblas_host_matrix *h, const float *a, int32_t m, int32_t lda, float *c,
+                                        int32_t ldc, float alpha, float beta);
+SBLAS_B200_API int32_t sblas_host_num_rows(const sblas_host_matrix *h);    /* NumRows()                 :39 */
+SBLAS_B200_API int32_t sblas_host_num_cols(const sblas_host_matrix *h);    /* NumCols()                 :40 */
+SBLAS_B200_API int32_t sblas_host_equal(sblas_host_matrix *a, sblas_host_matrix *b); /* operator==      :42 */
+SBLAS_B200_API int32_t sblas_host_selftest(void);                          /* SelfTest()                :43 (needs a GPU) */
+
+/* The compressed members (sparse-matrix.h:45-52), for uploads, slabs and structure tests. */
+SBLAS_B200_API int64_t sblas_host_entries(const sblas_host_matrix *h);
+SBLAS_B200_API int32_t sblas_host_nblocks(const sblas_host_matrix *h);
+SBLAS_B200_API int32_t sblas_host_table_size(const sblas_host_matrix *h);  /* valid entries T (val_table_ holds T+1) */
+/* Borrowed pointers, valid until the next CopyForm / Destroy / free.  Any may be NULL to skip. */
+SBLAS_B200_API void sblas_host_members(const sblas_host_matrix *h, const uint8_t **pos_index, const uint8_t **val_index,
+                                       const float **val_table, const int32_t **block_bounds,
+                                       const int32_t **block_index_bounds);
+/* The device matrix of this object on the current CUDA device (uploads on first use); NULL on failure. */
+SBLAS_B200_API sblas_b200_matrix *sblas_host_device_matrix(sblas_host_matrix *h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,235 @@
+"""Python face of the library: the reference's object interface and the raw device handle.
+
+``SparseMatrix`` mirrors ``sblas::SparseMatrix<uint8,uint8,float>`` (reference
+src/sparse/sparse-matrix.h:25-53): ``CopyForm / CopyTo / AddMatMat / NumRows / NumCols /
+Destroy`` with the reference's argument order, backed by the C++ host class of this build
+through ``include/sblas_b200_host.h``.  ``AddMatMat`` runs on the GPU.
+
+``DeviceMatrix`` wraps the opaque ``sblas_b200_matrix`` of ``include/sblas_b200.h``:
+uploads (whole matrix, panel-aligned slab, direct CSR), the host- and device-pointer
+products, and the structure read-backs used by the parity tests.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _capi
+
+
+def _ptr(x):
+    """void* of a numpy array / torch tensor / int / None."""
+    if x is None:
+        return None
+    if isinstance(x, int):
+        return C.c_void_p(x)
+    if isinstance(x, np.ndarray):
+        return x.ctypes.data_as(C.c_void_p)
+    if hasattr(x, "data_ptr"):
+        return C.c_void_p(x.data_ptr())
+    raise TypeError(type(x))
+
+
+def _f32c(a):
+    a = np.asarray(a)
+    if a.dtype != np.float32 or not a.flags.c_contiguous:
+        raise TypeError("expected a C-contiguous float32 array")
+    return a
+
+
+class DeviceMatrix:
+    """W = S^T resident on one GPU (opaque sblas_b200_matrix)."""
+
+    def __init__(self, handle, owned=True):
+        self._h = C.c_void_p(handle) if not isinstance(handle, C.c_void_p) else handle
+        self._owned = owned
+
+    # ---- construction -------------------------------------------------------------------
+    @classmethod
+    def upload(cls, pos, code, table, T, block_bounds, block_index_bounds, rows, cols, device=0,
+               col_begin=None, col_end=None):
+        """sblas_b200_upload / _upload_slab from the compressed members (numpy arrays)."""
+        L = _capi.lib()
+        pos = np.ascontiguousarray(pos, np.uint8); code = np.ascontiguousarray(code, np.uint8)
+        table = np.ascontiguousarray(table, np.float32)
+        bb = np.ascontiguousarray(block_bounds, np.int32).reshape(-1, 2)
+        bib = np.ascontiguousarray(block_index_bounds, np.int32).reshape(-1, 2)
+        out = C.c_void_p()
+        if col_begin is None and col_end is None:
+            rc = L.sblas_b200_upload(_ptr(pos), _ptr(code), pos.shape[0], _ptr(table), T, _ptr(bb), _ptr(bib),
+                                     bb.shape[0], rows, cols, device, C.byref(out))
+        else:
+            rc = L.sblas_b200_upload_slab(_ptr(pos), _ptr(code), pos.shape[0], _ptr(table), T, _ptr(bb), _ptr(bib),
+                                          bb.shape[0], rows, cols, int(col_begin or 0),
+                                          int(cols if col_end is None else col_end), device, C.byref(out))
+        _capi.check(rc)
+        return cls(out)
+
+    @classmethod
+    def upload_csr(cls, row_ptr, col, code, table, T, n, k, device=0):
+        L = _capi.lib()
+        row_ptr = np.ascontiguousarray(row_ptr, np.int32); col = np.ascontiguousarray(col, np.int32)
+        code = np.ascontiguousarray(code, np.uint8); table = np.ascontiguousarray(table, np.float32)
+        out = C.c_void_p()
+        _capi.check(L.sblas_b200_upload_csr(_ptr(row_ptr), _ptr(col), _ptr(code), _ptr(table), T, n, k, device,
+                                            C.byref(out)))
+        return cls(out)
+
+    def free(self):
+        if self._h and self._owned:
+            _capi.lib().sblas_b200_free(self._h)
+        self._h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+    # ---- queries ------------------------------------------------------------------------
+    def info(self):
+        inf = _capi.Info()
+        _capi.check(_capi.lib().sblas_b200_get_info(self._h, C.byref(inf)))
+        return inf
+
+    @property
+    def n(self):
+        return self.info().s_cols
+
+    @property
+    def k(self):
+        return self.info().s_rows
+
+    @property
+    def nnz(self):
+        return self.info().nnz
+
+    # ---- the product ----------------------------------------------------------------------
+    def addmatmat_host(self, a, m, lda, c, ldc, alpha, beta):
+        """C = beta*C + alpha*A*S on host buffers (numpy or pinned torch tensors), in place on c."""
+        _capi.check(_capi.lib().sblas_b200_addmatmat_host(self._h, _ptr(a), m, lda, _ptr(c), ldc, alpha, beta))
+        return c
+
+    def addmatmat_dev(self, d_a, m, lda, d_c, ldc, alpha, beta, stream=0):
+        """Same on device pointers (torch CUDA tensors or raw ints), enqueued on `stream` (cudaStream_t as int)."""
+        _capi.check(_capi.lib().sblas_b200_addmatmat_dev(self._h, _ptr(d_a), m, lda, _ptr(d_c), ldc, alpha, beta,
+                                                         C.c_void_p(stream) if stream else None))
+
+    def profile_begin(self):
+        _capi.check(_capi.lib().sblas_b200_profile_begin(self._h))
+
+    def profile_end(self):
+        """-> (summed dominant-kernel ms, bracketed launches)"""
+        ms = C.c_double(0.0); cnt = C.c_int64(0)
+        _capi.check(_capi.lib().sblas_b200_profile_end(self._h, C.byref(ms), C.byref(cnt)))
+        return ms.value, cnt.value
+
+    # ---- structure read-back ----------------------------------------------------------------
+    def decode_dense(self, stride, trans=False):
+        inf = self.info()
+        lead = inf.s_cols if trans else inf.s_rows
+        dense = np.full((lead, stride), np.float32(1.0), np.float32)
+        _capi.check(_capi.lib().sblas_b200_decode_dense(self._h, _ptr(dense), stride, int(bool(trans))))
+        return dense
+
+    def export_csr(self):
+        inf = self.info()
+        row_ptr = np.zeros(inf.s_cols + 1, np.int32)
+        col = np.zeros(inf.nnz, np.int32); code = np.zeros(inf.nnz, np.uint8)
+        _capi.check(_capi.lib().sblas_b200_export_csr(self._h, _ptr(row_ptr), _ptr(col), _ptr(code)))
+        return row_ptr, col, code
+
+
+def partition(block_bounds, block_index_bounds, cols, parts):
+    """sblas_b200_partition: nnz-balanced panel-aligned column splits, length parts+1."""
+    bb = np.ascontiguousarray(block_bounds, np.int32).reshape(-1, 2)
+    bib = np.ascontiguousarray(block_index_bounds, np.int32).reshape(-1, 2)
+    out = np.zeros(parts + 1, np.int32)
+    _capi.check(_capi.lib().sblas_b200_partition(_ptr(bb), _ptr(bib), bb.shape[0], cols, parts, _ptr(out)))
+    return out
+
+
+class SparseMatrix:
+    """sblas::SparseMatrix<uint8,uint8,float> (host object of this build)."""
+
+    NoTrans, Trans = 0, 1
+
+    def __init__(self, density_matrix=None, rows=0, cols=0, stride=0, vals=None, val_table_size=0, trans=0):
+        self._L = _capi.lib()
+        self._h = C.c_void_p(self._L.sblas_host_create())
+        if not self._h:
+            raise MemoryError("sblas_host_create")
+        if density_matrix is not None:
+            self.CopyForm(density_matrix, rows, cols, stride, vals, val_table_size, trans)
+
+    def __del__(self):
+        try:
+            if self._h:
+                self._L.sblas_host_free(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    def Destroy(self):
+        self._L.sblas_host_destroy(self._h)
+
+    def CopyForm(self, density_matrix, rows, cols, stride, vals, val_table_size, trans=0):
+        dm = np.ascontiguousarray(density_matrix, np.uint8).reshape(-1)
+        if dm.shape[0] < (rows - 1) * stride + cols and rows > 0:
+            raise ValueError("density_matrix smaller than rows x stride")
+        vals = np.ascontiguousarray(vals, np.float32).reshape(-1)
+        if vals.shape[0] < val_table_size:
+            raise ValueError("vals shorter than val_table_size")
+        rc = self._L.sblas_host_copyform(self._h, _ptr(dm), rows, cols, stride, _ptr(vals), val_table_size, int(trans))
+        if rc != _capi.OK:
+            raise ValueError("val_table_size outside [0, 255]")
+
+    def CopyTo(self, stride, trans=0):
+        """Returns the dense matrix (NumRows x stride, or NumCols x stride when trans)."""
+        lead = self.NumCols() if trans else self.NumRows()
+        dense = np.full((lead, stride), np.float32(1.0), np.float32)
+        self._L.sblas_host_copyto(self._h, _ptr(dense), stride, int(trans))
+        return dense
+
+    def AddMatMat(self, a, m, lda, c, ldc, alpha, beta):
+        """In place on c; a and c are host buffers (numpy float32 / pinned torch tensors)."""
+        _capi.check(self._L.sblas_host_addmatmat(self._h, _ptr(a), m, lda, _ptr(c), ldc, alpha, beta))
+        return c
+
+    def NumRows(self):
+        return self._L.sblas_host_num_rows(self._h)
+
+    def NumCols(self):
+        return self._L.sblas_host_num_cols(self._h)
+
+    def __eq__(self, other):
+        return isinstance(other, SparseMatrix) and bool(self._L.sblas_host_equal(self._h, other._h))
+
+    __hash__ = None
+
+    # ---- B200 additions -----------------------------------------------------------------
+    def members(self):
+        """Copies of the compressed members: (pos, code, table[T+1], T, block_bounds[nb,2], block_index_bounds[nb,2])."""
+        n = self._L.sblas_host_entries(self._h); nb = self._L.sblas_host_nblocks(self._h)
+        T = self._L.sblas_host_table_size(self._h)
+        p = [C.c_void_p() for _ in range(5)]
+        self._L.sblas_host_members(self._h, *[C.byref(x) for x in p])
+
+        def grab(ptr, count, dtype):
+            if not ptr.value or count == 0:
+                return np.zeros(count, dtype)
+            buf = (C.c_char * (count * np.dtype(dtype).itemsize)).from_address(ptr.value)
+            return np.frombuffer(buf, dtype=dtype, count=count).copy()
+
+        return (grab(p[0], n, np.uint8), grab(p[1], n, np.uint8), grab(p[2], T + 1 if T else 0, np.float32), T,
+                grab(p[3], 2 * nb, np.int32).reshape(-1, 2), grab(p[4], 2 * nb, np.int32).reshape(-1, 2))
+
+    def device_matrix(self):
+        """The uploaded matrix of this object on the current CUDA device (borrowed, owned by the object)."""
+        h = self._L.sblas_host_device_matrix(self._h)
+        if not h:
+            raise _capi.SblasError(_capi.ECUDA, self._L.sblas_b200_last_error().decode())
+        return DeviceMatrix(h, owned=False)
+
+    def upload_slab(self, col_begin, col_end, device=0):
+        pos, code, table, T, bb, bib = self.members()
+        return DeviceMatrix.upload(pos, code, table, T, bb, bib, self.NumRows(), self.NumCols(), device, col_begin, col_end)

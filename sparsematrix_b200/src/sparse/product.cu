@@ -1,0 +1,421 @@
+// product.cu -- the sparse x dense product on the device:  C = beta*C + alpha*A*S.
+//
+// Replaces the CPU micro-kernels the reference's AddMatMat drives
+// (reference src/sparse/sparse-matrix.cc:139-194 -> src/sparse/kernel.cc):
+//   sblas_beta_operation_kernel      kernel.cc:10-29    -> fused into the epilogues (scale_kernel when alpha == 0)
+//   sblas_trans_kernel               kernel.cc:31-187   -> transpose_in_kernel (A -> X = A^T) + smem-tile transposed stores
+//   sblas_kernel_operation_trans_ex  kernel.cc:771-800  -> done once at upload (src/utils/device_format.cu)
+//   sblas_kernel_mul_naive           kernel.cc:371-584  -> spmv_* (m == 1) and spmm_* (m >= 2) below
+//
+// North-star notation: Y[n x m] = W X with W = S^T (CSR, 1-byte codes), X = A^T, Y = C^T.
+// Arithmetic kept from the reference: the weight is fl(table[code]*alpha) (alpha folded
+// first, kernel.cc:791,794); C is scaled by beta only when beta != 1 (sparse-matrix.cc:149)
+// and then multiplies even for beta == 0; alpha == 0 means "scale only" (:152).
+#include <stdio.h>
+
+#include <algorithm>
+
+#include "device_matrix.h"
+
+namespace sblas_b200 {
+
+// ---- memory access helpers -------------------------------------------------------------
+// Index/value streams are read once: streaming loads (evict-first) keep them from pushing
+// the gathered x / X rows out of L2.
+__device__ __forceinline__ int4 ld_stream_int4(const int4 *p) { return __ldcs(p); }
+__device__ __forceinline__ uint32_t ld_stream_u32(const uint32_t *p) { return __ldcs(p); }
+
+// ---- K-scale: C *= beta (alpha == 0 path; sparse-matrix.cc:149-152) ----------------------
+__global__ void __launch_bounds__(256)
+scale_kernel(float *__restrict__ c, int m, int n, int ldc, float beta) {
+    const int j = blockIdx.x * 256 + threadIdx.x;
+    if (j >= n) return;
+    for (int i = blockIdx.y; i < m; i += gridDim.y) c[(size_t)i * ldc + j] *= beta;
+}
+
+// ---- K-spmv: row-split, sub-warp per row ---------------------------------------------------
+// LPR lanes share one W row.  A lane reads one aligned block of four column indices
+// (128-bit) and four codes (32-bit) per iteration and gathers four x values; partial
+// sums are combined with __shfl_xor.  Rows longer than long_threshold are left to the
+// split-row kernels below.
+template <int LPR>
+__global__ void __launch_bounds__(256)
+spmv_rows_kernel(const int32_t *__restrict__ row_ptr, const int4 *__restrict__ col4,
+                 const uint32_t *__restrict__ code4, const float *__restrict__ table, int T,
+                 const float *__restrict__ x, float *__restrict__ y, int n, float alpha, float beta,
+                 int long_threshold) {
+    __shared__ float s_tab[256];
+    s_tab[threadIdx.x] = (threadIdx.x < T) ? table[threadIdx.x] * alpha : 0.0f;    // val_table[code]*alpha
+    __syncthreads();
+    const int sub = threadIdx.x & (LPR - 1);
+    const int row = (int)(((size_t)blockIdx.x * 256 + threadIdx.x) / LPR);
+    int s = 0, e = 0;
+    if (row < n) { s = row_ptr[row]; e = row_ptr[row + 1]; }
+    const int len = e - s;
+    const bool mine = row < n && len <= long_threshold;
+    float acc = 0.0f;
+    if (mine && len > 0) {
+        const int b1 = (e - 1) >> 2;
+        for (int b = (s >> 2) + sub; b <= b1; b += LPR) {
+            const int4 c = ld_stream_int4(col4 + b);
+            const uint32_t cd = ld_stream_u32(code4 + b);
+            const int base = b << 2;
+            if (base >= s && base + 3 < e) {            // interior block: four independent gathers
+                const float x0 = __ldg(x + c.x), x1 = __ldg(x + c.y), x2 = __ldg(x + c.z), x3 = __ldg(x + c.w);
+                acc = fmaf(x0, s_tab[cd & 255u], acc);
+                acc = fmaf(x1, s_tab[(cd >> 8) & 255u], acc);
+                acc = fmaf(x2, s_tab[(cd >> 16) & 255u], acc);
+                acc = fmaf(x3, s_tab[cd >> 24], acc);
+            } else {                                    // first / last block of the row
+                if (base + 0 >= s && base + 0 < e) acc = fmaf(__ldg(x + c.x), s_tab[cd & 255u], acc);
+                if (base + 1 >= s && base + 1 < e) acc = fmaf(__ldg(x + c.y), s_tab[(cd >> 8) & 255u], acc);
+                if (base + 2 >= s && base + 2 < e) acc = fmaf(__ldg(x + c.z), s_tab[(cd >> 16) & 255u], acc);
+                if (base + 3 >= s && base + 3 < e) acc = fmaf(__ldg(x + c.w), s_tab[cd >> 24], acc);
+            }
+        }
+    }
+#pragma unroll
+    for (int o = LPR >> 1; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (mine && sub == 0) {
+        if (len == 0 && beta == 1.0f) return;           // column without entries, no scale: untouched
+        float c0 = y[row];
+        if (beta != 1.0f) c0 *= beta;
+        y[row] = c0 + acc;
+    }
+}
+
+// Split-row path: one CTA per segment (<= kLongSegment non-zeros) of a long row ...
+__global__ void __launch_bounds__(256)
+spmv_long_segment_kernel(const int32_t *__restrict__ seg_begin, const int32_t *__restrict__ seg_end,
+                         const int4 *__restrict__ col4, const uint32_t *__restrict__ code4,
+                         const float *__restrict__ table, int T, const float *__restrict__ x, float alpha,
+                         float *__restrict__ partial) {
+    __shared__ float s_tab[256];
+    __shared__ float s_red[8];
+    s_tab[threadIdx.x] = (threadIdx.x < T) ? table[threadIdx.x] * alpha : 0.0f;
+    __syncthreads();
+    const int s = seg_begin[blockIdx.x], e = seg_end[blockIdx.x];
+    float acc = 0.0f;
+    const int b1 = (e - 1) >> 2;
+    for (int b = (s >> 2) + threadIdx.x; b <= b1; b += 256) {
+        const int4 c = ld_stream_int4(col4 + b);
+        const uint32_t cd = ld_stream_u32(code4 + b);
+        const int base = b << 2;
+        if (base + 0 >= s && base + 0 < e) acc = fmaf(__ldg(x + c.x), s_tab[cd & 255u], acc);
+        if (base + 1 >= s && base + 1 < e) acc = fmaf(__ldg(x + c.y), s_tab[(cd >> 8) & 255u], acc);
+        if (base + 2 >= s && base + 2 < e) acc = fmaf(__ldg(x + c.z), s_tab[(cd >> 16) & 255u], acc);
+        if (base + 3 >= s && base + 3 < e) acc = fmaf(__ldg(x + c.w), s_tab[cd >> 24], acc);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.0f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) t += s_red[w];
+        partial[blockIdx.x] = t;
+    }
+}
+
+// ... and one thread per long row adds its segment sums in segment order (deterministic).
+__global__ void __launch_bounds__(128)
+spmv_long_finish_kernel(const int32_t *__restrict__ long_rows, const int32_t *__restrict__ long_seg_ptr,
+                        const float *__restrict__ partial, float *__restrict__ y, float beta, int n_long) {
+    const int i = blockIdx.x * 128 + threadIdx.x;
+    if (i >= n_long) return;
+    float t = 0.0f;
+    for (int s = long_seg_ptr[i]; s < long_seg_ptr[i + 1]; ++s) t += partial[s];
+    const int row = long_rows[i];
+    float c0 = y[row];
+    if (beta != 1.0f) c0 *= beta;
+    y[row] = c0 + t;
+}
+
+// ---- K-transpose-in: X[k][mp] = A^T, zero padded to mp (multiple of 4) ---------------------
+// The function of the reference's first sblas_trans_kernel call (sparse-matrix.cc:181).
+__global__ void __launch_bounds__(256)
+transpose_in_kernel(const float *__restrict__ a, int m, int k, int lda, float *__restrict__ xt, int mp) {
+    __shared__ float tile[32][33];
+    const int r0 = blockIdx.x * 32, i0 = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int ii = ty; ii < 32; ii += 8) {
+        const int i = i0 + ii, r = r0 + tx;
+        tile[ii][tx] = (i < m && r < k) ? a[(size_t)i * lda + r] : 0.0f;
+    }
+    __syncthreads();
+    for (int rr = ty; rr < 32; rr += 8) {
+        const int r = r0 + rr, i = i0 + tx;
+        if (r < k && i < mp) xt[(size_t)r * mp + i] = tile[tx][rr];
+    }
+}
+
+// ---- K-spmm (gather form): warp per W row, lanes over the dense columns --------------------
+// LPN lanes cover one non-zero's X row segment as float4 (tile of MT = 4*LPN dense
+// columns); a warp therefore works on 32/LPN non-zeros of its row at once ("slots"),
+// reduced with __shfl_xor at the end of the row.  X rows are read straight from L2/L1.
+// The 32 x MT result tile goes through shared memory so that C (row-major m x n, i.e.
+// Y^T) is written as 128-byte rows along j -- the function of the reference's two
+// per-panel C transposes (sparse-matrix.cc:184,189).
+template <int LPN>
+__global__ void __launch_bounds__(256)
+spmm_gather_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
+                   const uint8_t *__restrict__ code, const float *__restrict__ table, int T,
+                   const float *__restrict__ xt, int mp, float *__restrict__ c, int ldc, int n, int m,
+                   float alpha, float beta) {
+    constexpr int MT = 4 * LPN, SLOTS = 32 / LPN;
+    __shared__ float s_tab[256];
+    __shared__ float s_tile[32][MT + 1];
+    __shared__ int s_len[32];
+    s_tab[threadIdx.x] = (threadIdx.x < T) ? table[threadIdx.x] * alpha : 0.0f;
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int slot = lane / LPN, chunk = lane % LPN;
+    const int m0 = blockIdx.y * MT, j0 = blockIdx.x * 32;
+    const bool chunk_ok = m0 + chunk * 4 < mp;
+    const float *xbase = xt + m0 + chunk * 4;
+#pragma unroll 1
+    for (int rr = 0; rr < 4; ++rr) {
+        const int jl = warp * 4 + rr, j = j0 + jl;
+        int s = 0, e = 0;
+        if (j < n) { s = row_ptr[j]; e = row_ptr[j + 1]; }
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int base = s; base < e; base += 32) {
+            const int idx = base + lane;
+            int cc = 0;
+            float w = 0.0f;
+            if (idx < e) { cc = col[idx]; w = s_tab[code[idx]]; }
+            const int cnt = min(32, e - base);
+            for (int t = 0; t < cnt; t += SLOTS) {
+                const int r = __shfl_sync(0xffffffffu, cc, t + slot);
+                const float wv = __shfl_sync(0xffffffffu, w, t + slot);
+                if (chunk_ok) {
+                    const float4 xv = __ldg(reinterpret_cast<const float4 *>(xbase + (size_t)r * mp));
+                    acc.x = fmaf(wv, xv.x, acc.x);
+                    acc.y = fmaf(wv, xv.y, acc.y);
+                    acc.z = fmaf(wv, xv.z, acc.z);
+                    acc.w = fmaf(wv, xv.w, acc.w);
+                }
+            }
+        }
+#pragma unroll
+        for (int o = LPN; o < 32; o <<= 1) {
+            acc.x += __shfl_xor_sync(0xffffffffu, acc.x, o);
+            acc.y += __shfl_xor_sync(0xffffffffu, acc.y, o);
+            acc.z += __shfl_xor_sync(0xffffffffu, acc.z, o);
+            acc.w += __shfl_xor_sync(0xffffffffu, acc.w, o);
+        }
+        if (slot == 0) {
+            s_tile[jl][chunk * 4 + 0] = acc.x;
+            s_tile[jl][chunk * 4 + 1] = acc.y;
+            s_tile[jl][chunk * 4 + 2] = acc.z;
+            s_tile[jl][chunk * 4 + 3] = acc.w;
+        }
+        if (lane == 0) s_len[jl] = e - s;
+    }
+    __syncthreads();
+    const int jl = threadIdx.x & 31, j = j0 + jl;
+    if (j >= n) return;
+    if (s_len[jl] == 0 && beta == 1.0f) return;         // S column without entries and no scale: untouched
+    for (int i = threadIdx.x >> 5; i < MT; i += 8) {
+        const int gi = m0 + i;
+        if (gi >= m) break;
+        float *p = c + (size_t)gi * ldc + j;
+        float c0 = *p;
+        if (beta != 1.0f) c0 *= beta;
+        *p = c0 + s_tile[jl][i];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// dispatch
+// ---------------------------------------------------------------------------------------------
+// Brackets the dominant kernel with an event pair while the handle is being profiled.
+class KernelTimer {
+public:
+    KernelTimer(sblas_b200_matrix *mat, cudaStream_t stream) : mat_(mat), stream_(stream), on_(mat->profiling) {
+        if (!on_) return;
+        cudaEventCreate(&a_);
+        cudaEventCreate(&b_);
+        cudaEventRecord(a_, stream_);
+    }
+    ~KernelTimer() {
+        if (!on_) return;
+        cudaEventRecord(b_, stream_);
+        mat_->prof_events.push_back(std::make_pair(a_, b_));
+    }
+private:
+    sblas_b200_matrix *mat_;
+    cudaStream_t stream_;
+    bool on_;
+    cudaEvent_t a_ = nullptr, b_ = nullptr;
+};
+
+template <int LPR>
+static void launch_spmv_rows(const sblas_b200_matrix *mat, const float *x, float *y, float alpha, float beta,
+                             cudaStream_t stream) {
+    const size_t threads = (size_t)mat->n * LPR;
+    const unsigned grid = (unsigned)((threads + 255) / 256);
+    SB_LAUNCH(spmv_rows_kernel<LPR>, grid, 256, 0, stream, mat->d_row_ptr, reinterpret_cast<const int4 *>(mat->d_col),
+              reinterpret_cast<const uint32_t *>(mat->d_code), mat->d_table, mat->T, x, y, mat->n, alpha, beta,
+              mat->long_threshold);
+}
+
+static int run_spmv(sblas_b200_matrix *mat, const float *x, float *y, float alpha, float beta, cudaStream_t stream) {
+    {
+    KernelTimer timer(mat, stream);
+    switch (mat->spmv_lanes) {
+    case 1: launch_spmv_rows<1>(mat, x, y, alpha, beta, stream); break;
+    case 2: launch_spmv_rows<2>(mat, x, y, alpha, beta, stream); break;
+    case 4: launch_spmv_rows<4>(mat, x, y, alpha, beta, stream); break;
+    case 8: launch_spmv_rows<8>(mat, x, y, alpha, beta, stream); break;
+    case 16: launch_spmv_rows<16>(mat, x, y, alpha, beta, stream); break;
+    default: launch_spmv_rows<32>(mat, x, y, alpha, beta, stream); break;
+    }
+    }
+    SB_CHECK_LAUNCH();
+    if (mat->n_long) {
+        int rc = ensure_buffer(&mat->d_partial, &mat->partial_bytes, (size_t)mat->n_long_seg * 4);
+        if (rc != SBLAS_B200_OK) return rc;
+        SB_LAUNCH(spmv_long_segment_kernel, mat->n_long_seg, 256, 0, stream, mat->d_seg_begin, mat->d_seg_end,
+                  reinterpret_cast<const int4 *>(mat->d_col), reinterpret_cast<const uint32_t *>(mat->d_code),
+                  mat->d_table, mat->T, x, alpha, mat->d_partial);
+        SB_LAUNCH(spmv_long_finish_kernel, (mat->n_long + 127) / 128, 128, 0, stream, mat->d_long_rows,
+                  mat->d_long_seg_ptr, mat->d_partial, y, beta, mat->n_long);
+        SB_CHECK_LAUNCH();
+    }
+    return SBLAS_B200_OK;
+}
+
+template <int LPN>
+static void launch_spmm_gather(const sblas_b200_matrix *mat, const float *xt, int mp, float *c, int ldc, int m,
+                               float alpha, float beta, cudaStream_t stream) {
+    const dim3 grid((mat->n + 31) / 32, (m + 4 * LPN - 1) / (4 * LPN));
+    SB_LAUNCH(spmm_gather_kernel<LPN>, grid, 256, 0, stream, mat->d_row_ptr, mat->d_col, mat->d_code, mat->d_table,
+              mat->T, xt, mp, c, ldc, mat->n, m, alpha, beta);
+}
+
+static int run_spmm(sblas_b200_matrix *mat, const float *d_a, int m, int lda, float *d_c, int ldc, float alpha,
+                    float beta, cudaStream_t stream) {
+    const int mp = (m + 3) & ~3;
+    int rc = ensure_buffer(&mat->d_ws, &mat->ws_bytes, (size_t)mat->k * mp * 4);
+    if (rc != SBLAS_B200_OK) return rc;
+    const dim3 tgrid((mat->k + 31) / 32, (mp + 31) / 32);
+    SB_LAUNCH(transpose_in_kernel, tgrid, 256, 0, stream, d_a, m, mat->k, lda, mat->d_ws, mp);
+    KernelTimer timer(mat, stream);
+    if (mp <= 4) launch_spmm_gather<1>(mat, mat->d_ws, mp, d_c, ldc, m, alpha, beta, stream);
+    else if (mp <= 8) launch_spmm_gather<2>(mat, mat->d_ws, mp, d_c, ldc, m, alpha, beta, stream);
+    else if (mp <= 16) launch_spmm_gather<4>(mat, mat->d_ws, mp, d_c, ldc, m, alpha, beta, stream);
+    else if (mp <= 32) launch_spmm_gather<8>(mat, mat->d_ws, mp, d_c, ldc, m, alpha, beta, stream);
+    else if (mp <= 64) launch_spmm_gather<16>(mat, mat->d_ws, mp, d_c, ldc, m, alpha, beta, stream);
+    else launch_spmm_gather<32>(mat, mat->d_ws, mp, d_c, ldc, m, alpha, beta, stream);
+    SB_CHECK_LAUNCH();
+    return SBLAS_B200_OK;
+}
+
+int product_on_stream(sblas_b200_matrix *mat, const float *d_a, int32_t m, int32_t lda, float *d_c, int32_t ldc,
+                      float alpha, float beta, cudaStream_t stream) {
+    const int n = mat->n;
+    if (m == 0 || n == 0) return SBLAS_B200_OK;
+    if (alpha == 0.0f || mat->nnz == 0) {               // sparse-matrix.cc:149-152: only the beta scale remains
+        if (beta != 1.0f) {
+            const dim3 grid((n + 255) / 256, std::min(m, 1024));
+            SB_LAUNCH(scale_kernel, grid, 256, 0, stream, d_c, m, n, ldc, beta);
+            SB_CHECK_LAUNCH();
+        }
+        return SBLAS_B200_OK;
+    }
+    if (m == 1) return run_spmv(mat, d_a, d_c, alpha, beta, stream);
+    return run_spmm(mat, d_a, m, lda, d_c, ldc, alpha, beta, stream);
+}
+
+static int check_product_args(const sblas_b200_matrix *mat, const float *a, int32_t m, int32_t lda, const float *c,
+                              int32_t ldc) {
+    if (!mat) return fail(SBLAS_B200_EINVAL, "matrix handle is null");
+    if (m < 0) return fail(SBLAS_B200_EINVAL, "m = %d is negative", m);
+    if (m == 0 || mat->n == 0) return SBLAS_B200_OK;
+    if (!c) return fail(SBLAS_B200_EINVAL, "c is null");
+    if (!a && mat->k) return fail(SBLAS_B200_EINVAL, "a is null");
+    if (ldc < mat->n) return fail(SBLAS_B200_EINVAL, "ldc %d < n %d", ldc, mat->n);
+    if (lda < mat->k) return fail(SBLAS_B200_EINVAL, "lda %d < k %d", lda, mat->k);
+    return SBLAS_B200_OK;
+}
+
+}  // namespace sblas_b200
+
+using namespace sblas_b200;
+
+extern "C" {
+
+int sblas_b200_addmatmat_dev(sblas_b200_matrix *mat, const float *d_a, int32_t m, int32_t lda, float *d_c, int32_t ldc,
+                             float alpha, float beta, void *stream) {
+    int rc = check_product_args(mat, d_a, m, lda, d_c, ldc);
+    if (rc != SBLAS_B200_OK) return rc;
+    DeviceScope scope(mat->device);
+    if (!scope.ok()) return SBLAS_B200_ECUDA;
+    std::lock_guard<std::mutex> guard(mat->lock);
+    return product_on_stream(mat, d_a, m, lda, d_c, ldc, alpha, beta, static_cast<cudaStream_t>(stream));
+}
+
+int sblas_b200_profile_begin(sblas_b200_matrix *mat) {
+    if (!mat) return fail(SBLAS_B200_EINVAL, "matrix handle is null");
+    std::lock_guard<std::mutex> guard(mat->lock);
+    mat->profiling = true;
+    return SBLAS_B200_OK;
+}
+
+int sblas_b200_profile_end(sblas_b200_matrix *mat, double *total_ms, int64_t *launches) {
+    if (!mat) return fail(SBLAS_B200_EINVAL, "matrix handle is null");
+    DeviceScope scope(mat->device);
+    if (!scope.ok()) return SBLAS_B200_ECUDA;
+    std::lock_guard<std::mutex> guard(mat->lock);
+    mat->profiling = false;
+    double sum = 0.0;
+    int rc = SBLAS_B200_OK;
+    for (auto &ev : mat->prof_events) {
+        float ms = 0.0f;
+        cudaError_t e = cudaEventSynchronize(ev.second);
+        if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, ev.first, ev.second);
+        if (e != cudaSuccess && rc == SBLAS_B200_OK) rc = cuda_fail(e, "profile_end", __FILE__, __LINE__);
+        sum += ms;
+        cudaEventDestroy(ev.first);
+        cudaEventDestroy(ev.second);
+    }
+    if (total_ms) *total_ms = sum;
+    if (launches) *launches = (int64_t)mat->prof_events.size();
+    mat->prof_events.clear();
+    return rc;
+}
+
+int sblas_b200_addmatmat_host(sblas_b200_matrix *mat, const float *a, int32_t m, int32_t lda, float *c, int32_t ldc,
+                              float alpha, float beta) {
+    int rc = check_product_args(mat, a, m, lda, c, ldc);
+    if (rc != SBLAS_B200_OK) return rc;
+    if (m == 0 || mat->n == 0) return SBLAS_B200_OK;
+    DeviceScope scope(mat->device);
+    if (!scope.ok()) return SBLAS_B200_ECUDA;
+    std::lock_guard<std::mutex> guard(mat->lock);
+    const int n = mat->n, k = mat->k;
+    if (!mat->stream) SB_CUDA(cudaStreamCreateWithFlags(&mat->stream, cudaStreamNonBlocking));
+    const bool need_a = alpha != 0.0f && mat->nnz != 0;
+    if (need_a) {
+        rc = ensure_buffer(&mat->d_host_a, &mat->host_a_bytes, (size_t)m * k * 4);
+        if (rc != SBLAS_B200_OK) return rc;
+    }
+    rc = ensure_buffer(&mat->d_host_c, &mat->host_c_bytes, (size_t)m * n * 4);
+    if (rc != SBLAS_B200_OK) return rc;
+    if (beta == 1.0f && !need_a) return SBLAS_B200_OK;  // nothing changes C
+    if (need_a)
+        SB_CUDA(cudaMemcpy2DAsync(mat->d_host_a, (size_t)k * 4, a, (size_t)lda * 4, (size_t)k * 4, m,
+                                  cudaMemcpyHostToDevice, mat->stream));
+    SB_CUDA(cudaMemcpy2DAsync(mat->d_host_c, (size_t)n * 4, c, (size_t)ldc * 4, (size_t)n * 4, m,
+                              cudaMemcpyHostToDevice, mat->stream));
+    rc = product_on_stream(mat, mat->d_host_a, m, k, mat->d_host_c, n, alpha, beta, mat->stream);
+    if (rc != SBLAS_B200_OK) return rc;
+    SB_CUDA(cudaMemcpy2DAsync(c, (size_t)ldc * 4, mat->d_host_c, (size_t)n * 4, (size_t)n * 4, m,
+                              cudaMemcpyDeviceToHost, mat->stream));
+    SB_CUDA(cudaStreamSynchronize(mat->stream));
+    return SBLAS_B200_OK;
+}
+
+}  // extern "C"

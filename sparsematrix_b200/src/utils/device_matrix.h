@@ -1,0 +1,112 @@
+// device_matrix.h -- internal (C++/CUDA) view of the opaque sblas_b200_matrix handle,
+// error plumbing and launch accounting shared by src/utils (upload, allocation)
+// and src/sparse (product kernels).  Not installed; the public surface is
+// include/sblas_b200.h.
+#ifndef SBLAS_B200_DEVICE_MATRIX_H_
+#define SBLAS_B200_DEVICE_MATRIX_H_
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <atomic>
+#include <mutex>
+#include <utility>
+#include <vector>
+
+#include "sblas_b200.h"
+
+namespace sblas_b200 {
+
+// Panel geometry of the reference format (reference src/sparse/kernel.h:25-26).
+constexpr int kPanelShift = 8;
+constexpr int kPanelWidth = 1 << kPanelShift;
+constexpr int kPanelMask = kPanelWidth - 1;
+
+// SpMV plan constants (DESIGN.md "K-spmv").
+constexpr int kLongSegment = 8192;   // a long row is cut into segments of this many non-zeros, one CTA each
+
+void set_error(const char *fmt, ...);
+int fail(int code, const char *fmt, ...);
+int cuda_fail(cudaError_t e, const char *what, const char *file, int line);
+
+extern std::atomic<int64_t> g_kernel_launches;
+
+// RAII: make `device` current for the duration of an entry point, restore on exit.
+class DeviceScope {
+public:
+    explicit DeviceScope(int device);
+    ~DeviceScope();
+    bool ok() const { return ok_; }
+private:
+    int prev_;
+    bool ok_;
+};
+
+}  // namespace sblas_b200
+
+#define SB_CUDA(call)                                                                      \
+    do {                                                                                   \
+        cudaError_t sb_e_ = (call);                                                        \
+        if (sb_e_ != cudaSuccess) return ::sblas_b200::cuda_fail(sb_e_, #call, __FILE__, __LINE__); \
+    } while (0)
+
+// Launch + account.  Every kernel this library runs goes through here, so
+// sblas_b200_launch_count() is the number of our kernels that were enqueued.
+#define SB_LAUNCH(kernel, grid, block, smem, stream, ...)                                  \
+    do {                                                                                   \
+        kernel<<<(grid), (block), (smem), (stream)>>>(__VA_ARGS__);                        \
+        ::sblas_b200::g_kernel_launches.fetch_add(1, std::memory_order_relaxed);           \
+    } while (0)
+
+#define SB_CHECK_LAUNCH() SB_CUDA(cudaGetLastError())
+
+struct sblas_b200_matrix {
+    int device = 0;
+    int32_t k = 0;           // rows of S  = length of an X row index space
+    int32_t n = 0;           // columns of S held here = rows of W
+    int32_t col_begin = 0;   // first S column of the slab
+    int32_t T = 0;           // valid codebook entries
+    int64_t nnz = 0, fillers = 0, entries = 0;
+
+    // CSR of W = S^T, codebook-indexed values: 4 B column + 1 B code per non-zero.
+    // col/code are padded to a multiple of 4 entries (+4) so rows can be read as
+    // aligned 128-bit / 32-bit blocks.
+    int32_t *d_row_ptr = nullptr;   // [n+1]
+    int32_t *d_col = nullptr;       // [nnz_padded]
+    uint8_t *d_code = nullptr;      // [nnz_padded]
+    float *d_table = nullptr;       // [256], entries >= T are 0
+
+    // SpMV plan, chosen from the row-length histogram at upload.
+    int spmv_lanes = 8;             // sub-warp width for the row-split kernel
+    int32_t long_threshold = INT32_MAX;  // rows longer than this take the split-row path
+    int32_t n_long = 0, n_long_seg = 0, max_row_nnz = 0;
+    int32_t *d_long_rows = nullptr;     // [n_long]      row index
+    int32_t *d_long_seg_ptr = nullptr;  // [n_long+1]    first segment of each long row
+    int32_t *d_seg_begin = nullptr;     // [n_long_seg]  element range of a segment
+    int32_t *d_seg_end = nullptr;       // [n_long_seg]
+    int64_t row_len_hist[33] = {0};
+
+    // Per-handle workspace (X = A^T staging, split-row partials, host-path staging).
+    std::mutex lock;
+    float *d_ws = nullptr;      size_t ws_bytes = 0;       // X^T [k][m_pad]
+    float *d_partial = nullptr; size_t partial_bytes = 0;  // [n_long_seg * m]
+    float *d_host_a = nullptr;  size_t host_a_bytes = 0;   // host path: A on device
+    float *d_host_c = nullptr;  size_t host_c_bytes = 0;   // host path: C on device
+    cudaStream_t stream = nullptr;                          // host path stream
+    int64_t format_bytes = 0;
+
+    // sblas_b200_profile_begin/_end: event pairs around the dominant kernel
+    bool profiling = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t> > prof_events;
+};
+
+namespace sblas_b200 {
+// src/utils/device_format.cu
+int plan_spmv(sblas_b200_matrix *mat, const int32_t *h_row_ptr);
+int ensure_buffer(float **buf, size_t *have, size_t need);
+// src/sparse/product.cu
+int product_on_stream(sblas_b200_matrix *mat, const float *d_a, int32_t m, int32_t lda, float *d_c, int32_t ldc,
+                      float alpha, float beta, cudaStream_t stream);
+}  // namespace sblas_b200
+
+#endif

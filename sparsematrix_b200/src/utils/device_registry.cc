@@ -1,0 +1,55 @@
+#include "device_registry.h"
+
+#include <cuda_runtime_api.h>
+#include <stdio.h>
+
+#include <map>
+#include <mutex>
+#include <utility>
+
+#include "sblas_b200.h"
+
+namespace sblas {
+namespace device {
+
+namespace {
+std::mutex g_lock;
+// (owner, device ordinal) -> handle
+std::map<std::pair<const void *, int>, sblas_b200_matrix *> &table() {
+    static std::map<std::pair<const void *, int>, sblas_b200_matrix *> t;
+    return t;
+}
+}  // namespace
+
+sblas_b200_matrix *Acquire(const void *owner, const StreamView &v) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) {
+        printf("sblas_b200: no CUDA device available (this build has no CPU fallback)\n");
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> guard(g_lock);
+    auto key = std::make_pair(owner, dev);
+    auto it = table().find(key);
+    if (it != table().end()) return it->second;
+    sblas_b200_matrix *mat = nullptr;
+    const int rc = sblas_b200_upload(v.pos_index, v.val_index, v.entries, v.val_table, v.valid_table_size, v.block_bounds,
+                                     v.block_index_bounds, v.nblocks, v.rows, v.cols, dev, &mat);
+    if (rc != SBLAS_B200_OK) {
+        printf("sblas_b200: device upload failed (%d): %s\n", rc, sblas_b200_last_error());
+        return nullptr;
+    }
+    table()[key] = mat;
+    return mat;
+}
+
+void Evict(const void *owner) {
+    std::lock_guard<std::mutex> guard(g_lock);
+    auto &t = table();
+    for (auto it = t.lower_bound(std::make_pair(owner, -1)); it != t.end() && it->first.first == owner;) {
+        sblas_b200_free(it->second);
+        it = t.erase(it);
+    }
+}
+
+}  // namespace device
+}  // namespace sblas

@@ -1,0 +1,279 @@
+"""Parity tests proper: the CUDA path, called through the C ABI, against the oracle.
+
+Structure (upload -> CSR, decode) must be bit-exact.  Values: fp32, backward error
+  max |y - y64| / (|beta c| + |alpha| sum |a||s|) <= 1e-5   (north_star tolerance)
+with the reference arithmetic's own error computed alongside.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import sparsematrix_b200 as sb
+from sparsematrix_b200 import _capi, gen
+from oracle import oracle as O
+from helpers import assert_bits_equal, golden_names, golden_stream, load_golden
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-5      # backward error, fp32 vs fp64 statement
+
+
+def check_values(got, s, a, m, lda, c0, ldc, alpha, beta, what=""):
+    n = s.cols
+    y64, bound = O.addmatmat_f64(s, a, m, lda, c0, ldc, alpha, beta)
+    back, norm, _ = O.error_measures(got, m, n, ldc, y64, bound)
+    want = O.addmatmat(s, a, m, lda, c0.copy(), ldc, alpha, beta)
+    rback, rnorm, _ = O.error_measures(want, m, n, ldc, y64, bound)
+    assert back <= TOL, f"{what}: backward error {back:.3e} > {TOL} (reference arithmetic: {rback:.3e})"
+    assert norm <= 1e-4, f"{what}: normwise error {norm:.3e} (reference {rnorm:.3e})"
+    # padding columns of C (ldc > n) must be untouched
+    if ldc > n:
+        assert_bits_equal(got.reshape(m, ldc)[:, n:], c0.reshape(m, ldc)[:, n:], what + " ldc padding")
+    return back, rback
+
+
+def upload(s, **kw):
+    return sb.DeviceMatrix.upload(s.pos, s.code, s.table, s.T, s.block_bounds, s.block_index_bounds, s.rows, s.cols, **kw)
+
+
+# ------------------------------------------------------------------ golden dumps of the reference
+@pytest.mark.parametrize("name", golden_names())
+def test_golden_structure_and_values(name):
+    g = load_golden(name)
+    s = golden_stream(g)
+    dev = upload(s)
+    inf = dev.info()
+    assert (inf.s_rows, inf.s_cols, inf.table_size) == (s.rows, s.cols, s.T)
+    assert inf.fillers == int((s.code >= s.T).sum()) and inf.nnz + inf.fillers == s.entries
+    row_ptr, col, code = dev.export_csr()
+    o_row_ptr, o_col, o_code, _ = O.stream_to_csr(s)
+    assert np.array_equal(row_ptr, o_row_ptr) and np.array_equal(col, o_col) and np.array_equal(code, o_code)
+    assert_bits_equal(dev.decode_dense(int(g["stride_notrans"]), False), g["dense_notrans"], "decode NoTrans")
+    assert_bits_equal(dev.decode_dense(int(g["stride_trans"]), True), g["dense_trans"], "decode Trans")
+    m, lda, ldc = int(g["m"]), int(g["lda"]), int(g["ldc"])
+    alpha, beta = float(g["alpha"]), float(g["beta"])
+    got = dev.addmatmat_host(g["a"], m, lda, g["c_in"].copy(), ldc, alpha, beta)
+    check_values(got, s, g["a"], m, lda, g["c_in"], ldc, alpha, beta, name)
+    # the reference's own result is inside the same tolerance of ours
+    y64, bound = O.addmatmat_f64(s, g["a"], m, lda, g["c_in"], ldc, alpha, beta)
+    assert O.error_measures(g["c_out"], m, s.cols, ldc, y64, bound)[0] <= TOL
+    if alpha == 0.0:        # scale only: same single rounding as the reference -> identical bits
+        assert_bits_equal(got, g["c_out"], "alpha == 0")
+
+
+def test_kat_selftest_through_device_path():
+    # sparse-matrix.cc:209-313 re-stated in the host class and run on the GPU
+    assert sb.lib().sblas_host_selftest() == 1
+    g = load_golden("kat1")
+    S = sb.SparseMatrix(g["codes"], 3, 2, 2, g["vals"], 8, 0)
+    c = S.AddMatMat(g["a"], 1, 3, g["c_in"].copy(), 2, 1.3, 2.0)
+    assert abs(c[0] - 92.513) <= 1e-3 and abs(c[1] - 44.6) <= 1e-3
+
+
+# ------------------------------------------------------------------ seeded sweeps
+SHAPES = [
+    # n, k, density
+    (257, 300, 0.10),
+    (1023, 2047, 0.25),      # the harness's default shape (blas_test.cc:32)
+    (1024, 512, 0.01),       # fillers
+    (512, 4096, 0.001),      # filler dominated
+    (300, 64, 1.0),          # fully dense
+    (4096, 4096, 0.01),      # BASELINE config 1 (m = 1 below)
+]
+MS = [1, 2, 3, 7, 8, 9, 31, 117, 128]
+SCALARS = [(1.0, 1.0), (1.0, 0.0), (1.3, 2.0), (1.8, 1.2), (0.0, 0.5)]
+
+
+@pytest.mark.parametrize("shape", SHAPES)
+def test_structure_bit_exact(shape):
+    n, k, dens = shape
+    codes = gen.codes_bernoulli(n, k, dens, seed=n * 7 + k)
+    tab = gen.codebook()
+    S = sb.SparseMatrix(codes, n, k, k, tab, 255, 1)
+    s = O.copyform(codes, n, k, k, tab, 255, True)
+    dev = S.device_matrix()
+    row_ptr, col, code = dev.export_csr()
+    o_row_ptr, o_col, o_code, fill = O.stream_to_csr(s)
+    assert dev.info().fillers == fill
+    assert np.array_equal(row_ptr, o_row_ptr) and np.array_equal(col, o_col) and np.array_equal(code, o_code)
+    assert_bits_equal(dev.decode_dense(n + 3, False), O.copyto(s, n + 3, False), "decode NoTrans")
+    assert_bits_equal(dev.decode_dense(k, True), O.copyto(s, k, True), "decode Trans")
+
+
+@pytest.mark.parametrize("shape", SHAPES[:5])
+def test_values_all_m_and_scalars(shape):
+    n, k, dens = shape
+    codes = gen.codes_bernoulli(n, k, dens, seed=n * 7 + k)
+    tab = gen.codebook()
+    S = sb.SparseMatrix(codes, n, k, k, tab, 255, 1)
+    s = O.copyform(codes, n, k, k, tab, 255, True)
+    worst = 0.0
+    for mi, m in enumerate(MS):
+        alpha, beta = SCALARS[mi % len(SCALARS)]
+        lda, ldc = k + (mi % 3), n + (mi % 2) * 5
+        a = gen.dense_uniform((m, lda), 2 + mi)
+        c0 = gen.dense_uniform((m, ldc), 3 + mi)
+        got = S.AddMatMat(a, m, lda, c0.copy(), ldc, alpha, beta)
+        back, _ = check_values(got, s, a, m, lda, c0, ldc, alpha, beta, f"{shape} m={m} a={alpha} b={beta}")
+        worst = max(worst, back)
+    assert worst <= TOL
+
+
+@pytest.mark.parametrize("scal", SCALARS)
+@pytest.mark.parametrize("m", [1, 8, 128])
+def test_values_all_scalars(m, scal):
+    alpha, beta = scal
+    n, k = 700, 333
+    codes = gen.codes_bernoulli(n, k, 0.05, seed=41)
+    codes[256:512, :] = 255                              # an unrecorded panel: those columns only get the scale
+    tab = gen.codebook()
+    S = sb.SparseMatrix(codes, n, k, k, tab, 255, 1)
+    s = O.copyform(codes, n, k, k, tab, 255, True)
+    a = gen.dense_uniform((m, k), 42); c0 = gen.dense_uniform((m, n), 43)
+    c0[0, 300] = -0.0
+    got = S.AddMatMat(a, m, k, c0.copy(), n, alpha, beta)
+    check_values(got, s, a, m, k, c0, n, alpha, beta, f"m={m} a={alpha} b={beta}")
+    want = O.addmatmat(s, a, m, k, c0.copy(), n, alpha, beta)
+    # columns of the empty panel: one rounding at most, identical to the reference bit for bit
+    assert_bits_equal(got.reshape(m, n)[:, 256:512], want.reshape(m, n)[:, 256:512], "empty panel columns")
+
+
+def test_config1_spmv_4096_one_percent():
+    # BASELINE.json configs[0]: random 4096 x 4096, 1 % density, m = 1
+    n = k = 4096
+    codes = gen.codes_bernoulli(n, k, 0.01, seed=11)
+    tab = gen.codebook()
+    S = sb.SparseMatrix(codes, n, k, k, tab, 255, 1)
+    s = O.copyform(codes, n, k, k, tab, 255, True)
+    a = gen.dense_uniform((1, k), 2); c0 = gen.dense_uniform((1, n), 3)
+    got = S.AddMatMat(a, 1, k, c0.copy(), n, 1.0, 1.0)
+    back, rback = check_values(got, s, a, 1, k, c0, n, 1.0, 1.0, "config 1")
+    print(f"config1 backward error: gpu {back:.2e} reference arithmetic {rback:.2e}")
+
+
+def test_config2_spmm_4096_ninety_percent_sparse_m128():
+    # BASELINE.json configs[1]: pruned weight 4096 x 4096 at 90 % sparsity x dense 4096 x 128
+    n = k = 4096; m = 128
+    codes = gen.codes_bernoulli(n, k, 0.10, seed=12)
+    tab = gen.codebook()
+    S = sb.SparseMatrix(codes, n, k, k, tab, 255, 1)
+    s = O.copyform(codes, n, k, k, tab, 255, True)
+    a = gen.dense_uniform((m, k), 2); c0 = gen.dense_uniform((m, n), 3)
+    got = S.AddMatMat(a, m, k, c0.copy(), n, 1.0, 1.0)
+    back, rback = check_values(got, s, a, m, k, c0, n, 1.0, 1.0, "config 2")
+    print(f"config2 backward error: gpu {back:.2e} reference arithmetic {rback:.2e}")
+
+
+def test_nan_in_c_propagates_with_beta_zero():
+    # the reference multiplies by beta even when it is 0 (sparse-matrix.cc:149-151): NaN stays NaN
+    n, k = 300, 100
+    codes = gen.codes_bernoulli(n, k, 0.2, seed=9)
+    S = sb.SparseMatrix(codes, n, k, k, gen.codebook(), 255, 1)
+    for m in (1, 5):
+        a = gen.dense_uniform((m, k), 1); c0 = gen.dense_uniform((m, n), 2)
+        c0[0, 7] = np.nan; c0[m - 1, 290] = np.inf
+        got = S.AddMatMat(a, m, k, c0.copy(), n, 1.0, 0.0).reshape(m, n)
+        assert np.isnan(got[0, 7]) and np.isnan(got[m - 1, 290])
+        assert np.isfinite(np.delete(got.reshape(-1), [7, (m - 1) * n + 290])).all()
+
+
+# ------------------------------------------------------------------ direct CSR (shapes the panel format cannot hold)
+def test_csr_upload_matches_stream_upload():
+    n, k = 1000, 777
+    codes = gen.codes_bernoulli(n, k, 0.03, seed=5)
+    tab = gen.codebook()
+    s = O.copyform(codes, n, k, k, tab, 255, True)
+    row_ptr, col, code, _ = O.stream_to_csr(s)
+    d1 = upload(s)
+    d2 = sb.DeviceMatrix.upload_csr(row_ptr, col, code, tab, 255, n, k)
+    for m in (1, 6):
+        a = gen.dense_uniform((m, k), 1); c0 = gen.dense_uniform((m, n), 2)
+        y1 = d1.addmatmat_host(a, m, k, c0.copy(), n, 1.3, 2.0)
+        y2 = d2.addmatmat_host(a, m, k, c0.copy(), n, 1.3, 2.0)
+        assert_bits_equal(y1, y2, "stream upload vs CSR upload")
+
+
+def test_powerlaw_spmv_with_long_rows():
+    # scaled-down BASELINE config 4: skewed rows incl. rows far above the split-row threshold
+    n = k = 1 << 17
+    row_ptr, col, code = gen.powerlaw_csr(n, k, seed=14, x_min=8, cap=1 << 16)
+    tab = gen.codebook()
+    dev = sb.DeviceMatrix.upload_csr(row_ptr, col, code, tab, 255, n, k)
+    inf = dev.info()
+    assert inf.long_rows > 0 and inf.max_row_nnz > 8192
+    a = gen.dense_uniform((1, k), 1); c0 = gen.dense_uniform((1, n), 2)
+    for alpha, beta in ((1.0, 1.0), (1.3, 2.0)):
+        got = dev.addmatmat_host(a, 1, k, c0.copy(), n, alpha, beta)
+        y64, bound = O.addmatmat_csr_f64(row_ptr, col, code, tab, 255, n, k, a, 1, k, c0, n, alpha, beta)
+        back, norm, _ = O.error_measures(got, 1, n, n, y64, bound)
+        want = O.addmatmat_csr(row_ptr, col, code, tab, 255, n, k, a, 1, k, c0.copy(), n, alpha, beta)
+        rback = O.error_measures(want, 1, n, n, y64, bound)[0]
+        assert back <= TOL, (back, rback)
+        got2 = dev.addmatmat_host(a, 1, k, c0.copy(), n, alpha, beta)
+        assert_bits_equal(got, got2, "run-to-run determinism")
+    # SpMM on the same skewed matrix
+    a = gen.dense_uniform((4, k), 1); c0 = gen.dense_uniform((4, n), 2)
+    got = dev.addmatmat_host(a, 4, k, c0.copy(), n, 1.0, 1.0)
+    y64, bound = O.addmatmat_csr_f64(row_ptr, col, code, tab, 255, n, k, a, 4, k, c0, n, 1.0, 1.0)
+    assert O.error_measures(got, 4, n, n, y64, bound)[0] <= TOL
+
+
+def test_bad_csr_and_bad_stream_are_rejected():
+    tab = gen.codebook()
+    row_ptr = np.array([0, 2, 3], np.int32); col = np.array([0, 9, 1], np.int32); code = np.array([1, 2, 3], np.uint8)
+    with pytest.raises(sb.SblasError) as ei:
+        sb.DeviceMatrix.upload_csr(row_ptr, col, code, tab, 255, 2, 5)       # column 9 >= k
+    assert ei.value.code == _capi.EFORMAT
+    # a stream whose positions run past the matrix
+    pos = np.array([200, 255, 255], np.uint8); cd = np.array([0, 1, 2], np.uint8)
+    with pytest.raises(sb.SblasError):
+        sb.DeviceMatrix.upload(pos, cd, tab, 255, [[0, 0]], [[0, 3]], 2, 256)    # rows = 2 but pos reaches row 2
+    with pytest.raises(sb.SblasError):
+        d = sb.DeviceMatrix.upload(np.array([1], np.uint8), np.array([0], np.uint8), tab, 255, [[0, 0]], [[0, 1]], 4, 8)
+        d.addmatmat_host(np.zeros(4, np.float32), 1, 2, np.zeros(8, np.float32), 8, 1.0, 1.0)   # lda < k
+
+
+# ------------------------------------------------------------------ device-pointer entry point + slabs
+def test_device_pointer_entry_matches_host_entry():
+    import torch
+    n, k, m = 900, 600, 33
+    codes = gen.codes_bernoulli(n, k, 0.07, seed=8)
+    S = sb.SparseMatrix(codes, n, k, k, gen.codebook(), 255, 1)
+    dev = S.device_matrix()
+    a = gen.dense_uniform((m, k + 4), 1); c0 = gen.dense_uniform((m, n + 8), 2)
+    want = dev.addmatmat_host(a, m, k + 4, c0.copy(), n + 8, 1.3, 2.0)
+    d_a = torch.from_numpy(a).cuda(); d_c = torch.from_numpy(c0.copy()).cuda()
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        dev.addmatmat_dev(d_a, m, k + 4, d_c, n + 8, 1.3, 2.0, stream=st.cuda_stream)
+    st.synchronize()
+    assert_bits_equal(d_c.cpu().numpy(), want, "dev vs host entry point")
+
+
+@pytest.mark.parametrize("parts", [2, 3, 8])
+def test_virtual_shards_concatenate_to_unsharded_result(parts):
+    # run the slabs one after another on one device; row-split kernels make each
+    # output row independent of the partition, so the concatenation is bit-identical
+    n, k = 2048 + 100, 500
+    codes = gen.codes_bernoulli(n, k, 0.05, seed=77)
+    S = sb.SparseMatrix(codes, n, k, k, gen.codebook(), 255, 1)
+    _, _, _, _, bb, bib = S.members()
+    splits = sb.partition(bb, bib, n, parts)
+    for m in (1, 16):
+        a = gen.dense_uniform((m, k), 1); c0 = gen.dense_uniform((m, n), 2)
+        whole = S.AddMatMat(a, m, k, c0.copy(), n, 1.3, 2.0)
+        pieces = c0.copy()
+        tot_nnz = 0
+        for g in range(parts):
+            lo, hi = int(splits[g]), int(splits[g + 1])
+            if hi == lo:
+                continue
+            slab = S.upload_slab(lo, hi)
+            tot_nnz += slab.info().nnz
+            view = pieces.reshape(m, n)[:, lo:]                 # c points at column col_begin, ldc stays n
+            ptr = view.ctypes.data
+            _capi.check(sb.lib().sblas_b200_addmatmat_host(slab._h, a.ctypes.data_as(C.c_void_p), m, k,
+                                                           C.c_void_p(ptr), n, 1.3, 2.0))
+        assert tot_nnz == S.device_matrix().info().nnz
+        assert_bits_equal(pieces, whole, f"virtual shards parts={parts} m={m}")

@@ -1,0 +1,110 @@
+"""CPU-side tests of the product's host logic (no GPU, no compute calls on the device):
+the C-ABI library loads and exports every declared symbol, the host class builds and
+decodes the compressed format bit-for-bit like the reference (golden dumps + oracle),
+and the slab partitioner behaves."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import sparsematrix_b200 as sb
+from sparsematrix_b200 import _capi, gen
+from oracle import oracle as O
+from helpers import assert_bits_equal, golden_names, load_golden
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    declared = set()
+    for hdr in ("sblas_b200.h", "sblas_b200_host.h"):
+        text = open(os.path.join(ROOT, "include", hdr)).read()
+        declared |= set(re.findall(r"SBLAS_B200_API[^;(]*?\b(sblas_\w+)\s*\(", text))
+    assert len(declared) >= 25
+    L = C.CDLL(_capi.LIB_PATH)
+    for name in sorted(declared):
+        assert hasattr(L, name), f"{name} declared in include/ but not exported"
+    assert declared == set(_capi.SYMBOLS), "ctypes table and headers disagree"
+    assert sb.lib().sblas_b200_abi_version() == 1
+
+
+def test_product_does_not_reference_oracle():
+    # the oracle is test infrastructure: nothing under sparsematrix_b200/ may import or link it
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "sparsematrix_b200")):
+        for f in files:
+            if f.endswith((".py", ".cc", ".cu", ".h", "Makefile")):
+                text = open(os.path.join(dirpath, f), errors="replace").read()
+                assert "liboracle" not in text and "sblas_oracle" not in text and "from oracle" not in text, (dirpath, f)
+
+
+@pytest.mark.parametrize("name", golden_names())
+def test_host_class_matches_reference_dump(name):
+    g = load_golden(name)
+    S = sb.SparseMatrix()
+    S.CopyForm(g["codes"], int(g["rows"]), int(g["cols"]), int(g["stride"]), g["vals"], int(g["T"]), int(g["trans"]))
+    assert (S.NumRows(), S.NumCols()) == (int(g["s_rows"]), int(g["s_cols"]))
+    pos, code, table, T, bb, bib = S.members()
+    assert np.array_equal(pos, g["pos"]) and np.array_equal(code, g["code"])
+    assert_bits_equal(table, g["table"], "val_table_")
+    assert np.array_equal(bb, g["block_bounds"]) and np.array_equal(bib, g["block_index_bounds"])
+    assert_bits_equal(S.CopyTo(int(g["stride_notrans"]), 0), g["dense_notrans"], "CopyTo NoTrans")
+    assert_bits_equal(S.CopyTo(int(g["stride_trans"]), 1), g["dense_trans"], "CopyTo Trans")
+
+
+@pytest.mark.parametrize("trans", [0, 1])
+@pytest.mark.parametrize("shape", [(1023, 511, 512, 63, 0.25), (300, 700, 700, 255, 0.01), (5, 1, 1, 3, 0.9)])
+def test_host_class_matches_oracle(shape, trans):
+    rows, cols, stride, T, dens = shape
+    codes = np.full((rows, stride), 255, np.uint8)
+    codes[:, :cols] = gen.codes_bernoulli(rows, cols, dens, seed=rows + cols, T=T)
+    tab = gen.codebook(T, 2)
+    S = sb.SparseMatrix(codes, rows, cols, stride, tab, T, trans)
+    s = O.copyform(codes, rows, cols, stride, tab, T, bool(trans))
+    pos, code, table, T2, bb, bib = S.members()
+    assert s.same_as(O.Stream(pos, code, table, T2, bb, bib, S.NumRows(), S.NumCols()))
+    assert_bits_equal(S.CopyTo(stride, trans), O.copyto(s, stride, bool(trans)), "CopyTo")
+    S2 = sb.SparseMatrix(codes, rows, cols, stride, tab, T, trans)
+    assert S == S2
+    S2.Destroy()
+    assert (S2.NumRows(), S2.NumCols()) == (0, 0) and not (S == S2)
+
+
+def test_empty_table_and_bad_table_size():
+    S = sb.SparseMatrix(np.zeros(12, np.uint8), 3, 4, 4, np.zeros(1, np.float32), 0)
+    assert (S.NumRows(), S.NumCols()) == (0, 0)          # sparse-matrix.cc:26
+    with pytest.raises(ValueError):
+        S.CopyForm(np.zeros(12, np.uint8), 3, 4, 4, np.zeros(300, np.float32), 256)
+
+
+def test_partition_balances_entries_on_panel_boundaries():
+    n, k = 2048, 300
+    codes = gen.codes_bernoulli(n, k, 0.05, seed=5)
+    codes[0:512] = 255                                      # two empty leading panels
+    codes[1536:1792, ::2] = 255                             # one half-density panel
+    S = sb.SparseMatrix(codes, n, k, k, gen.codebook(), 255, 1)
+    _, _, _, _, bb, bib = S.members()
+    for parts in (1, 2, 3, 4, 8, 16):
+        sp = sb.partition(bb, bib, n, parts)
+        assert sp[0] == 0 and sp[-1] == n and np.all(np.diff(sp) >= 0)
+        assert all(int(x) % 256 == 0 for x in sp[1:-1])
+    sp = sb.partition(bb, bib, n, 2)
+    cnt = np.zeros(8, np.int64)
+    for (r, c), (s, e) in zip(bb, bib):
+        cnt[c // 256] = e - s
+    left = cnt[: sp[1] // 256].sum()
+    best = min(abs(cnt[:b].sum() * 2 - cnt.sum()) for b in range(9))
+    assert abs(left * 2 - cnt.sum()) == best
+    # cols not a multiple of 256
+    sp = sb.partition(bb[:1], bib[:1], 700, 4)
+    assert sp[-1] == 700 and np.all(np.diff(sp) >= 0)
+
+
+def test_argument_errors_are_reported_without_a_device():
+    L = sb.lib()
+    out = C.c_void_p()
+    rc = L.sblas_b200_upload(None, None, 5, None, 300, None, None, 0, 4, 4, 0, C.byref(out))
+    assert rc == _capi.EINVAL and b"valid_table_size" in L.sblas_b200_last_error()
+    rc = L.sblas_b200_addmatmat_host(None, None, 1, 1, None, 1, 1.0, 1.0)
+    assert rc == _capi.EINVAL

@@ -12,6 +12,7 @@
 // first, kernel.cc:791,794); C is scaled by beta only when beta != 1 (sparse-matrix.cc:149)
 // and then multiplies even for beta == 0; alpha == 0 means "scale only" (:152).
 #include <stdio.h>
+#include <stdlib.h>
 
 #include <algorithm>
 
@@ -80,7 +81,7 @@ spmv_rows_kernel(const int32_t *__restrict__ row_ptr, const int4 *__restrict__ c
         if (len == 0 && beta == 1.0f) return;           // column without entries, no scale: untouched
         float c0 = y[row];
         if (beta != 1.0f) c0 *= beta;
-        y[row] = c0 + acc;
+        y[row] = len ? c0 + acc : c0;                   // no entry: exactly the scaled value (keeps -0)
     }
 }
 
@@ -186,15 +187,26 @@ spmm_gather_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restric
             float w = 0.0f;
             if (idx < e) { cc = col[idx]; w = s_tab[code[idx]]; }
             const int cnt = min(32, e - base);
-            for (int t = 0; t < cnt; t += SLOTS) {
-                const int r = __shfl_sync(0xffffffffu, cc, t + slot);
-                const float wv = __shfl_sync(0xffffffffu, w, t + slot);
-                if (chunk_ok) {
-                    const float4 xv = __ldg(reinterpret_cast<const float4 *>(xbase + (size_t)r * mp));
-                    acc.x = fmaf(wv, xv.x, acc.x);
-                    acc.y = fmaf(wv, xv.y, acc.y);
-                    acc.z = fmaf(wv, xv.z, acc.z);
-                    acc.w = fmaf(wv, xv.w, acc.w);
+            // U independent gathers in flight per lane before the first FMA needs its operand
+            constexpr int U = 4;
+            for (int t = 0; t < cnt; t += SLOTS * U) {
+                float4 xv[U];
+                float wv[U];
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const int src = t + u * SLOTS + slot;           // entry of this slot in step u
+                    const int r = __shfl_sync(0xffffffffu, cc, src & 31);
+                    wv[u] = __shfl_sync(0xffffffffu, w, src & 31);
+                    xv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (chunk_ok && src < cnt) xv[u] = __ldg(reinterpret_cast<const float4 *>(xbase + (size_t)r * mp));
+                    else wv[u] = 0.0f;
+                }
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    acc.x = fmaf(wv[u], xv[u].x, acc.x);
+                    acc.y = fmaf(wv[u], xv[u].y, acc.y);
+                    acc.z = fmaf(wv[u], xv[u].z, acc.z);
+                    acc.w = fmaf(wv[u], xv[u].w, acc.w);
                 }
             }
         }
@@ -223,7 +235,7 @@ spmm_gather_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restric
         float *p = c + (size_t)gi * ldc + j;
         float c0 = *p;
         if (beta != 1.0f) c0 *= beta;
-        *p = c0 + s_tile[jl][i];
+        *p = s_len[jl] ? c0 + s_tile[jl][i] : c0;        // no entry: exactly the scaled value (keeps -0)
     }
 }
 
@@ -297,6 +309,16 @@ static void launch_spmm_gather(const sblas_b200_matrix *mat, const float *xt, in
 
 static int run_spmm(sblas_b200_matrix *mat, const float *d_a, int m, int lda, float *d_c, int ldc, float alpha,
                     float beta, cudaStream_t stream) {
+    // large m: X staged through shared memory (src/sparse/spmm_tile.cu) once the tile format exists
+    int tile_min_m = 17;
+    if (const char *env = getenv("SBLAS_B200_TILE_MIN_M")) tile_min_m = atoi(env);
+    if (m >= tile_min_m) {
+        if (mat->tile_state == 0) {
+            const int brc = build_tile_format(mat, stream);
+            if (brc != SBLAS_B200_OK) return brc;
+        }
+        if (mat->tile_state == 1) return run_spmm_tile(mat, d_a, m, lda, d_c, ldc, alpha, beta, stream);
+    }
     const int mp = (m + 3) & ~3;
     int rc = ensure_buffer(&mat->d_ws, &mat->ws_bytes, (size_t)mat->k * mp * 4);
     if (rc != SBLAS_B200_OK) return rc;

@@ -1,0 +1,264 @@
+// spmm_tile.cu -- K-spmm (tile form): SpMM with the dense operand staged through shared memory.
+//
+// Y[n x m] = W X.  A CTA owns NWARPS*16 W rows and a tile of MT = 32*NF4 dense columns; it walks
+// the X rows in chunks of 255.  Chunk c of the X tile (255 x MT fp32, contiguous in the tile-major
+// X^T workspace) is brought in by ONE bulk asynchronous copy (cp.async.bulk -> mbarrier complete_tx,
+// the TMA engine; no thread moves data) into a ring of STAGES buffers, while the warps consume the
+// previous chunk.  Row 255 of every buffer is an all-zero row that padding entries point at.
+//
+// A warp owns one group of 16 W rows (src/utils/tile_format.cu).  Its entries for all chunks form
+// one contiguous stream of 80-byte blocks, read with a two-block look-ahead.  Lanes are arranged as
+// 4 slots x 8 column lanes: a slot handles every fourth entry of a row, a column lane holds
+// float4 #f of the MT dense columns -- one step of a warp is 4 entries x MT columns: per lane one
+// LDS.128 per float4 and 4 FFMA.  This replaces the reference's AXPY micro-kernel
+// (kernel.cc:371-584: cc[0..m) += aa[0..m) * val) with the roles of "contiguous m" kept: the m
+// dense values of one X row are contiguous in shared memory exactly like aa[] is contiguous there.
+//
+// Accumulators stay in registers across the whole k loop (16 rows x NF4 float4 per lane); the four
+// slot partials are combined with __shfl_xor at the end, and the result tile goes through shared
+// memory so that C (row-major m x n = Y^T) is written in 128-byte rows -- the function of the
+// reference's per-panel C transposes (sparse-matrix.cc:184,189).  beta is applied there
+// (only when != 1, sparse-matrix.cc:149), alpha is folded into the weights first (kernel.cc:791).
+#include <stdlib.h>
+
+#include <algorithm>
+
+#include "device_matrix.h"
+
+namespace sblas_b200 {
+
+namespace {
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// global -> shared bulk copy, completion counted in bytes on an mbarrier (TMA engine; SASS UBLKCP)
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+struct Block {      // one slot's share of an 80-byte block: four weights, four X-row offsets
+    float4 w;
+    uint32_t r;
+};
+__device__ __forceinline__ Block load_block(const uint8_t *__restrict__ blocks, int64_t bi, int slot) {
+    Block b;
+    const uint8_t *p = blocks + bi * kBlockBytes;
+    b.w = __ldg(reinterpret_cast<const float4 *>(p) + slot);
+    b.r = __ldg(reinterpret_cast<const uint32_t *>(p + 64) + slot);
+    return b;
+}
+
+}  // namespace
+
+// ---- K-transpose-in (tile-major): xt[tile][r][il] = A[tile*MT + il][r], zero beyond m ----------
+__global__ void __launch_bounds__(256)
+transpose_in_tiled_kernel(const float *__restrict__ a, int m, int k, int lda, float *__restrict__ xt, int k_alloc,
+                          int MT) {
+    __shared__ float tile[32][33];
+    const int r0 = blockIdx.x * 32, i0 = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int ii = ty; ii < 32; ii += 8) {
+        const int i = i0 + ii, r = r0 + tx;
+        tile[ii][tx] = (i < m && r < k) ? a[(size_t)i * lda + r] : 0.0f;
+    }
+    __syncthreads();
+    const int i = i0 + tx;                              // dense column; MT is a multiple of 32
+    const int t = i / MT, il = i - t * MT;
+    for (int rr = ty; rr < 32; rr += 8) {
+        const int r = r0 + rr;
+        if (r < k) xt[((size_t)t * k_alloc + r) * MT + il] = tile[tx][rr];
+    }
+}
+
+template <int NWARPS, int NF4, int STAGES>
+__global__ void __launch_bounds__(NWARPS * 32, 1)
+spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__ grp_ptr,
+                 const uint16_t *__restrict__ seg_len, const int32_t *__restrict__ row_ptr, int ngroups, int nchunks,
+                 int n, const float *__restrict__ xt, int k_alloc, float *__restrict__ c, int ldc, int m, float alpha,
+                 float beta) {
+    constexpr int MT = 32 * NF4, RB = NWARPS * kTileRows, NT = NWARPS * 32;
+    constexpr int STAGE_FLOATS = 256 * MT;                       // 255 data rows + the zero row
+    constexpr uint32_t CHUNK_BYTES = kTileK * MT * 4;
+    extern __shared__ __align__(128) uint8_t smem_raw[];
+    float *xs = reinterpret_cast<float *>(smem_raw);
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + (size_t)STAGES * STAGE_FLOATS * 4);
+    __shared__ int s_len[RB];
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int slot = lane >> 3, c8 = lane & 7;
+    const int j0 = blockIdx.x * RB;
+    const float *xt_tile = xt + (size_t)blockIdx.y * k_alloc * MT;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) mbar_init(&full[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    for (int s = 0; s < STAGES; ++s)                              // the zero row of every stage
+        for (int i = threadIdx.x; i < MT; i += NT) xs[(size_t)s * STAGE_FLOATS + kTileK * MT + i] = 0.0f;
+    for (int i = threadIdx.x; i < RB; i += NT) {
+        const int j = j0 + i;
+        s_len[i] = j < n ? row_ptr[j + 1] - row_ptr[j] : 0;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES && s < nchunks; ++s) {
+            mbar_expect_tx(&full[s], CHUNK_BYTES);
+            bulk_g2s(xs + (size_t)s * STAGE_FLOATS, xt_tile + (size_t)s * kTileK * MT, CHUNK_BYTES, &full[s]);
+        }
+    }
+
+    const int g = blockIdx.x * NWARPS + warp;
+    const bool live = g < ngroups;
+    float4 acc[kTileRows][NF4];
+#pragma unroll
+    for (int rr = 0; rr < kTileRows; ++rr)
+#pragma unroll
+        for (int f = 0; f < NF4; ++f) acc[rr][f] = make_float4(0.f, 0.f, 0.f, 0.f);
+
+    // the warp's block stream: contiguous over all chunks of its group
+    int64_t bi = live ? grp_ptr[(int64_t)g * nchunks] : 0;
+    Block cur = load_block(blocks, bi, slot), nx1 = load_block(blocks, bi + 1, slot);
+    int len_next = (live && lane < kTileRows) ? seg_len[((int64_t)g * nchunks) * kTileRows + lane] : 0;
+
+    for (int ch = 0; ch < nchunks; ++ch) {
+        const int stage = ch % STAGES;
+        const int my_len = len_next;
+        if (live && lane < kTileRows && ch + 1 < nchunks)
+            len_next = seg_len[((int64_t)g * nchunks + ch + 1) * kTileRows + lane];
+        mbar_wait(&full[stage], (uint32_t)((ch / STAGES) & 1));
+        const float *xst = xs + (size_t)stage * STAGE_FLOATS + c8 * 4;
+#pragma unroll
+        for (int rr = 0; rr < kTileRows; ++rr) {
+            const int len = __shfl_sync(0xffffffffu, my_len, rr);
+            const int nit = (len + 3) >> 2;
+            for (int it = 0; it < nit; it += 4) {
+                float4 w = cur.w;
+                const uint32_t r4 = cur.r;
+                cur = nx1;
+                nx1 = load_block(blocks, bi + 2, slot);
+                ++bi;
+                if (alpha != 1.0f) { w.x *= alpha; w.y *= alpha; w.z *= alpha; w.w *= alpha; }
+                const float wt[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    if (it + t < nit) {
+                        const float *xr = xst + ((r4 >> (8 * t)) & 255u) * MT;
+#pragma unroll
+                        for (int f = 0; f < NF4; ++f) {
+                            const float4 xv = *reinterpret_cast<const float4 *>(xr + 32 * f);
+                            acc[rr][f].x = fmaf(wt[t], xv.x, acc[rr][f].x);
+                            acc[rr][f].y = fmaf(wt[t], xv.y, acc[rr][f].y);
+                            acc[rr][f].z = fmaf(wt[t], xv.z, acc[rr][f].z);
+                            acc[rr][f].w = fmaf(wt[t], xv.w, acc[rr][f].w);
+                        }
+                    }
+                }
+            }
+        }
+        __syncthreads();                                         // every warp is done with this stage
+        if (threadIdx.x == 0 && ch + STAGES < nchunks) {
+            mbar_expect_tx(&full[stage], CHUNK_BYTES);
+            bulk_g2s(xs + (size_t)stage * STAGE_FLOATS, xt_tile + (size_t)(ch + STAGES) * kTileK * MT, CHUNK_BYTES,
+                     &full[stage]);
+        }
+    }
+
+    // combine the four slots, stage the RB x MT tile in shared memory (the X ring is free now)
+    float *tile = xs;                                            // [RB][MT + 1]
+#pragma unroll
+    for (int rr = 0; rr < kTileRows; ++rr)
+#pragma unroll
+        for (int f = 0; f < NF4; ++f) {
+            float4 v = acc[rr][f];
+            v.x += __shfl_xor_sync(0xffffffffu, v.x, 8);  v.y += __shfl_xor_sync(0xffffffffu, v.y, 8);
+            v.z += __shfl_xor_sync(0xffffffffu, v.z, 8);  v.w += __shfl_xor_sync(0xffffffffu, v.w, 8);
+            v.x += __shfl_xor_sync(0xffffffffu, v.x, 16); v.y += __shfl_xor_sync(0xffffffffu, v.y, 16);
+            v.z += __shfl_xor_sync(0xffffffffu, v.z, 16); v.w += __shfl_xor_sync(0xffffffffu, v.w, 16);
+            if (slot == 0) {
+                float *p = tile + (size_t)(warp * kTileRows + rr) * (MT + 1) + 32 * f + c8 * 4;
+                p[0] = v.x; p[1] = v.y; p[2] = v.z; p[3] = v.w;
+            }
+        }
+    __syncthreads();
+    const int m0 = blockIdx.y * MT;
+    for (int idx = threadIdx.x; idx < RB * MT; idx += NT) {
+        const int i = idx / RB, jl = idx - i * RB;
+        const int gi = m0 + i, j = j0 + jl;
+        if (gi >= m || j >= n) continue;
+        const int len = s_len[jl];
+        if (len == 0 && beta == 1.0f) continue;                  // S column without entries, no scale: untouched
+        float *p = c + (size_t)gi * ldc + j;
+        float c0 = *p;
+        if (beta != 1.0f) c0 *= beta;
+        *p = len ? c0 + tile[(size_t)jl * (MT + 1) + i] : c0;
+    }
+}
+
+template <int NWARPS, int NF4, int STAGES>
+static int launch_tile(sblas_b200_matrix *mat, const float *xt, int k_alloc, float *d_c, int ldc, int m, float alpha,
+                       float beta, cudaStream_t stream) {
+    constexpr int MT = 32 * NF4;
+    const size_t smem = (size_t)STAGES * 256 * MT * 4 + STAGES * 8;
+    static bool configured = false;                              // per template instance
+    if (!configured) {
+        SB_CUDA(cudaFuncSetAttribute(spmm_tile_kernel<NWARPS, NF4, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)smem));
+        configured = true;
+    }
+    const dim3 grid((mat->tile_ngroups + NWARPS - 1) / NWARPS, (m + MT - 1) / MT);
+    SB_LAUNCH((spmm_tile_kernel<NWARPS, NF4, STAGES>), grid, NWARPS * 32, smem, stream, mat->d_tile_blocks,
+              mat->d_grp_ptr, mat->d_seg_len, mat->d_row_ptr, mat->tile_ngroups, mat->tile_nchunks, mat->n, xt, k_alloc,
+              d_c, ldc, m, alpha, beta);
+    SB_CHECK_LAUNCH();
+    return SBLAS_B200_OK;
+}
+
+// Variant selection: "<warps><f4>" from SBLAS_B200_TILE (experiments), else by shape.
+int run_spmm_tile(sblas_b200_matrix *mat, const float *d_a, int m, int lda, float *d_c, int ldc, float alpha,
+                  float beta, cudaStream_t stream) {
+    int nwarps = 8, nf4 = (m > 32) ? 2 : 1;
+    if (const char *env = getenv("SBLAS_B200_TILE")) {
+        if (env[0] == '4' || env[0] == '8') nwarps = env[0] - '0';
+        if (env[1] == '1' || env[1] == '2') nf4 = env[1] - '0';
+    }
+    const int MT = 32 * nf4;
+    const int ntiles = (m + MT - 1) / MT;
+    const int k_alloc = mat->tile_nchunks * kTileK;
+    int rc = ensure_buffer(&mat->d_ws, &mat->ws_bytes, (size_t)ntiles * k_alloc * MT * 4);
+    if (rc != SBLAS_B200_OK) return rc;
+    const dim3 tgrid((mat->k + 31) / 32, ntiles * MT / 32);
+    SB_LAUNCH(transpose_in_tiled_kernel, tgrid, 256, 0, stream, d_a, m, mat->k, lda, mat->d_ws, k_alloc, MT);
+    SB_CHECK_LAUNCH();
+    struct Timer {                                                // event pair around the dominant kernel when profiling
+        sblas_b200_matrix *mat; cudaStream_t st; cudaEvent_t a = nullptr, b = nullptr;
+        Timer(sblas_b200_matrix *m_, cudaStream_t s_) : mat(m_), st(s_) {
+            if (mat->profiling) { cudaEventCreate(&a); cudaEventCreate(&b); cudaEventRecord(a, st); }
+        }
+        ~Timer() { if (a) { cudaEventRecord(b, st); mat->prof_events.push_back(std::make_pair(a, b)); } }
+    } timer(mat, stream);
+    if (nwarps == 8 && nf4 == 2) return launch_tile<8, 2, 2>(mat, mat->d_ws, k_alloc, d_c, ldc, m, alpha, beta, stream);
+    if (nwarps == 8 && nf4 == 1) return launch_tile<8, 1, 3>(mat, mat->d_ws, k_alloc, d_c, ldc, m, alpha, beta, stream);
+    if (nwarps == 4 && nf4 == 2) return launch_tile<4, 2, 2>(mat, mat->d_ws, k_alloc, d_c, ldc, m, alpha, beta, stream);
+    return launch_tile<4, 1, 3>(mat, mat->d_ws, k_alloc, d_c, ldc, m, alpha, beta, stream);
+}
+
+}  // namespace sblas_b200

@@ -240,11 +240,26 @@ seg_scatter_kernel(const uint8_t *__restrict__ pos, const uint8_t *__restrict__ 
     }
 }
 
+int exclusive_scan_i32(const int32_t *d_in, int n, int32_t *d_out, cudaStream_t stream) {
+    SB_LAUNCH(row_ptr_scan_kernel, 1, 1024, 0, stream, d_in, n, d_out);
+    SB_CHECK_LAUNCH();
+    return SBLAS_B200_OK;
+}
+
 // CSR validation for direct uploads: every column index inside [0, k), every code < T.
 __global__ void csr_validate_kernel(const int32_t *__restrict__ col, const uint8_t *__restrict__ code, int64_t nnz,
                                     int k, int T, int *__restrict__ bad) {
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nnz; i += (int64_t)gridDim.x * blockDim.x)
         if ((unsigned)col[i] >= (unsigned)k || code[i] >= T) atomicOr(bad, 1);
+}
+
+// bit 1 of *bad: some row's columns are not strictly ascending (the tile format then stays off)
+__global__ void csr_sorted_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col, int n,
+                                  int *__restrict__ bad) {
+    const int j = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (j >= n) return;
+    for (int e = row_ptr[j] + 1 + lane; e < row_ptr[j + 1]; e += 32)
+        if (col[e] <= col[e - 1]) atomicOr(bad, 2);
 }
 
 // K-decode: CSR(W) -> dense, the function of CopyTo (sparse-matrix.cc:101-137).  Warp per W row.
@@ -345,6 +360,7 @@ static void release(sblas_b200_matrix *mat) {
     if (!mat) return;
     cudaFree(mat->d_row_ptr); cudaFree(mat->d_col); cudaFree(mat->d_code); cudaFree(mat->d_table);
     cudaFree(mat->d_long_rows); cudaFree(mat->d_long_seg_ptr); cudaFree(mat->d_seg_begin); cudaFree(mat->d_seg_end);
+    cudaFree(mat->d_tile_blocks); cudaFree(mat->d_grp_ptr); cudaFree(mat->d_seg_len);
     cudaFree(mat->d_ws); cudaFree(mat->d_partial); cudaFree(mat->d_host_a); cudaFree(mat->d_host_c);
     if (mat->stream) cudaStreamDestroy(mat->stream);
     delete mat;
@@ -562,11 +578,13 @@ int sblas_b200_upload_csr(const int32_t *row_ptr, const int32_t *col, const uint
         if (e == cudaSuccess) e = cudaMemset(d_bad, 0, 4);
         if (e == cudaSuccess) {
             SB_LAUNCH(csr_validate_kernel, 148 * 8, 256, 0, 0, mat->d_col, mat->d_code, nnz, k, T, d_bad);
+            SB_LAUNCH(csr_sorted_kernel, (n + 7) / 8, 256, 0, 0, mat->d_row_ptr, mat->d_col, n, d_bad);
             e = cudaMemcpy(&h_bad, d_bad, 4, cudaMemcpyDeviceToHost);
         }
         cudaFree(d_bad);
         if (e != cudaSuccess) rc = cuda_fail(e, "CSR validation", __FILE__, __LINE__);
-        else if (h_bad) rc = fail(SBLAS_B200_EFORMAT, "CSR holds a column index outside [0,%d) or a code >= %d", k, T);
+        else if (h_bad & 2) mat->csr_sorted = false;
+        if (e == cudaSuccess && (h_bad & 1)) rc = fail(SBLAS_B200_EFORMAT, "CSR holds a column index outside [0,%d) or a code >= %d", k, T);
     }
     if (rc == SBLAS_B200_OK) rc = plan_spmv(mat, row_ptr);
     if (rc != SBLAS_B200_OK) { release(mat); return rc; }

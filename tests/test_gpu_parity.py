@@ -253,8 +253,8 @@ def test_device_pointer_entry_matches_host_entry():
 
 @pytest.mark.parametrize("parts", [2, 3, 8])
 def test_virtual_shards_concatenate_to_unsharded_result(parts):
-    # run the slabs one after another on one device; row-split kernels make each
-    # output row independent of the partition, so the concatenation is bit-identical
+    # run the slabs one after another on one device; every output row is computed
+    # by its own slab alone, so the concatenation equals the unsharded result (bit-identical for SpMM)
     n, k = 2048 + 100, 500
     codes = gen.codes_bernoulli(n, k, 0.05, seed=77)
     S = sb.SparseMatrix(codes, n, k, k, gen.codebook(), 255, 1)
@@ -276,4 +276,11 @@ def test_virtual_shards_concatenate_to_unsharded_result(parts):
             _capi.check(sb.lib().sblas_b200_addmatmat_host(slab._h, a.ctypes.data_as(C.c_void_p), m, k,
                                                            C.c_void_p(ptr), n, 1.3, 2.0))
         assert tot_nnz == S.device_matrix().info().nnz
-        assert_bits_equal(pieces, whole, f"virtual shards parts={parts} m={m}")
+        if m == 1:
+            # SpMV reads aligned 4-entry blocks, so which lane sums which entry depends on where a
+            # row starts in the slab's own arrays: same values to rounding, not to the bit
+            s = O.copyform(codes, n, k, k, gen.codebook(), 255, True)
+            check_values(pieces, s, a, m, k, c0, n, 1.3, 2.0, f"virtual shards parts={parts} m=1")
+            assert np.max(np.abs(pieces - whole)) <= 1e-5 * np.max(np.abs(whole))
+        else:
+            assert_bits_equal(pieces, whole, f"virtual shards parts={parts} m={m}")

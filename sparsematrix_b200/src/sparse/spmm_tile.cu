@@ -1,20 +1,21 @@
 // spmm_tile.cu -- K-spmm (tile form): SpMM with the dense operand staged through shared memory.
 //
-// Y[n x m] = W X.  A CTA owns NWARPS*16 W rows and a tile of MT = 32*NF4 dense columns; it walks
+// Y[n x m] = W X.  A CTA owns NWARPS*8 W rows and a tile of MT = 32*NF4 dense columns; it walks
 // the X rows in chunks of 255.  Chunk c of the X tile (255 x MT fp32, contiguous in the tile-major
 // X^T workspace) is brought in by ONE bulk asynchronous copy (cp.async.bulk -> mbarrier complete_tx,
 // the TMA engine; no thread moves data) into a ring of STAGES buffers, while the warps consume the
 // previous chunk.  Row 255 of every buffer is an all-zero row that padding entries point at.
 //
-// A warp owns one group of 16 W rows (src/utils/tile_format.cu).  Its entries for all chunks form
-// one contiguous stream of 80-byte blocks, read with a two-block look-ahead.  Lanes are arranged as
+// A warp owns one group of 8 W rows (src/utils/tile_format.cu).  Its entries for all chunks form
+// one contiguous stream of 80-byte blocks, which also arrives by bulk copies into a private
+// two-half ring in shared memory (a warp's entry fetch would otherwise sit on the L2/HBM latency).  Lanes are arranged as
 // 4 slots x 8 column lanes: a slot handles every fourth entry of a row, a column lane holds
 // float4 #f of the MT dense columns -- one step of a warp is 4 entries x MT columns: per lane one
 // LDS.128 per float4 and 4 FFMA.  This replaces the reference's AXPY micro-kernel
 // (kernel.cc:371-584: cc[0..m) += aa[0..m) * val) with the roles of "contiguous m" kept: the m
 // dense values of one X row are contiguous in shared memory exactly like aa[] is contiguous there.
 //
-// Accumulators stay in registers across the whole k loop (16 rows x NF4 float4 per lane); the four
+// Accumulators stay in registers across the whole k loop (8 rows x NF4 float4 per lane); the four
 // slot partials are combined with __shfl_xor at the end, and the result tile goes through shared
 // memory so that C (row-major m x n = Y^T) is written in 128-byte rows -- the function of the
 // reference's per-panel C transposes (sparse-matrix.cc:184,189).  beta is applied there
@@ -55,16 +56,29 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
                  : "memory");
 }
 
-struct Block {      // one slot's share of an 80-byte block: four weights, four X-row offsets
-    float4 w;
-    uint32_t r;
-};
-__device__ __forceinline__ Block load_block(const uint8_t *__restrict__ blocks, int64_t bi, int slot) {
-    Block b;
-    const uint8_t *p = blocks + bi * kBlockBytes;
-    b.w = __ldg(reinterpret_cast<const float4 *>(p) + slot);
-    b.r = __ldg(reinterpret_cast<const uint32_t *>(p + 64) + slot);
-    return b;
+__device__ __forceinline__ void bulk_g2s_addr(uint32_t dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+constexpr int kRingHalf = 32;                                   // blocks per half of a warp's ring
+constexpr int kRingBytes = 2 * kRingHalf * kBlockBytes;        // 5120 B per warp
+
+// The warp has just read the last block of a ring half (`consumed` blocks read so far): refill
+// that half with the blocks one ring ahead, then make sure the half it moves into has landed.
+__device__ __noinline__ void ring_turn(uint32_t ring, uint64_t *wbar, const uint8_t *stream, int consumed, int total,
+                                       int lane) {
+    const int done_half = ((consumed - 1) / kRingHalf) & 1;
+    __syncwarp();
+    const int nxt = consumed + kRingHalf;                        // first block of the refill
+    if (lane == 0 && nxt < total) {
+        const int cnt = min(kRingHalf, total - nxt);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        mbar_expect_tx(&wbar[done_half], (uint32_t)cnt * kBlockBytes);
+        bulk_g2s_addr(ring + done_half * kRingHalf * kBlockBytes, stream + (size_t)nxt * kBlockBytes,
+                      (uint32_t)cnt * kBlockBytes, &wbar[done_half]);
+    }
+    if (consumed < total) mbar_wait(&wbar[done_half ^ 1], (uint32_t)((consumed / (2 * kRingHalf)) & 1));
 }
 
 }  // namespace
@@ -100,7 +114,9 @@ spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__
     constexpr uint32_t CHUNK_BYTES = kTileK * MT * 4;
     extern __shared__ __align__(128) uint8_t smem_raw[];
     float *xs = reinterpret_cast<float *>(smem_raw);
-    uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + (size_t)STAGES * STAGE_FLOATS * 4);
+    uint8_t *ring_base = smem_raw + (size_t)STAGES * STAGE_FLOATS * 4;                   // [NWARPS][kRingBytes]
+    uint64_t *full = reinterpret_cast<uint64_t *>(ring_base + (size_t)NWARPS * kRingBytes);  // [STAGES]
+    uint64_t *wfull = full + STAGES;                                                      // [NWARPS][2]
     __shared__ int s_len[RB];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -110,6 +126,7 @@ spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; ++s) mbar_init(&full[s], 1);
+        for (int s = 0; s < 2 * NWARPS; ++s) mbar_init(&wfull[s], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     for (int s = 0; s < STAGES; ++s)                              // the zero row of every stage
@@ -134,42 +151,77 @@ spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__
 #pragma unroll
         for (int f = 0; f < NF4; ++f) acc[rr][f] = make_float4(0.f, 0.f, 0.f, 0.f);
 
-    // the warp's block stream: contiguous over all chunks of its group
-    int64_t bi = live ? grp_ptr[(int64_t)g * nchunks] : 0;
-    Block cur = load_block(blocks, bi, slot), nx1 = load_block(blocks, bi + 1, slot);
+    // The warp's block stream -- contiguous over all chunks of its group -- flows through a private
+    // two-half ring in shared memory.  Each half is filled by one bulk copy; when the warp has read
+    // the last block of a half, lane 0 refills that half (ring_turn, off the hot path).
+    const int64_t s0 = live ? grp_ptr[(int64_t)g * nchunks] : 0;
+    const int total = live ? (int)(grp_ptr[(int64_t)(g + 1) * nchunks] - s0) : 0;
+    const uint8_t *ring_ptr = ring_base + (size_t)warp * kRingBytes;
+    const uint32_t ring = smem_u32(ring_ptr);
+    uint64_t *wbar = wfull + 2 * warp;
+    const uint8_t *stream = blocks + s0 * kBlockBytes;
+    if (lane == 0) {
+        for (int h = 0; h < 2; ++h) {
+            const int cnt = min(kRingHalf, total - h * kRingHalf);
+            if (cnt > 0) {
+                mbar_expect_tx(&wbar[h], (uint32_t)cnt * kBlockBytes);
+                bulk_g2s_addr(ring + h * kRingHalf * kBlockBytes, stream + (size_t)h * kRingHalf * kBlockBytes,
+                              (uint32_t)cnt * kBlockBytes, &wbar[h]);
+            }
+        }
+    }
+    // One block is always held in registers ahead of the one being used (`cur`); `reads` counts the
+    // blocks taken out of the ring, `left` those still unread in the half `rp` points into.
+    int reads = 0, left = kRingHalf;
+    const uint8_t *rp = ring_ptr + slot * 16;                    // this slot's read pointer into the ring
+    float4 cur_w = make_float4(0.f, 0.f, 0.f, 0.f);
+    uint32_t cur_r = 0u;
+    auto read_next = [&](float4 &w, uint32_t &r4) {
+        if (reads < total) {
+            w = *reinterpret_cast<const float4 *>(rp);
+            r4 = *reinterpret_cast<const uint32_t *>(rp + 64 - slot * 12);
+            rp += kBlockBytes;
+            ++reads;
+            if (--left == 0) {                                   // that was the last block of a half
+                ring_turn(ring, wbar, stream, reads, total, lane);
+                left = kRingHalf;
+                if (((reads / kRingHalf) & 1) == 0) rp = ring_ptr + slot * 16;
+            }
+        }
+    };
+    if (total > 0) mbar_wait(&wbar[0], 0u);
+    read_next(cur_w, cur_r);
     int len_next = (live && lane < kTileRows) ? seg_len[((int64_t)g * nchunks) * kTileRows + lane] : 0;
 
     for (int ch = 0; ch < nchunks; ++ch) {
         const int stage = ch % STAGES;
-        const int my_len = len_next;
+        const int my_nit = (len_next + 3) >> 2;                  // steps (4 entries each) of my row in this chunk
         if (live && lane < kTileRows && ch + 1 < nchunks)
             len_next = seg_len[((int64_t)g * nchunks + ch + 1) * kTileRows + lane];
         mbar_wait(&full[stage], (uint32_t)((ch / STAGES) & 1));
-        const float *xst = xs + (size_t)stage * STAGE_FLOATS + c8 * 4;
+        const uint8_t *xst = reinterpret_cast<const uint8_t *>(xs + (size_t)stage * STAGE_FLOATS + c8 * 4);
 #pragma unroll
         for (int rr = 0; rr < kTileRows; ++rr) {
-            const int len = __shfl_sync(0xffffffffu, my_len, rr);
-            const int nit = (len + 3) >> 2;
+            const int nit = __shfl_sync(0xffffffffu, my_nit, rr);
+#pragma unroll 1
             for (int it = 0; it < nit; it += 4) {
-                float4 w = cur.w;
-                const uint32_t r4 = cur.r;
-                cur = nx1;
-                nx1 = load_block(blocks, bi + 2, slot);
-                ++bi;
+                float4 w = cur_w;
+                const uint32_t r4 = cur_r;
+                read_next(cur_w, cur_r);                         // next block's weights/offsets, ahead of use
                 if (alpha != 1.0f) { w.x *= alpha; w.y *= alpha; w.z *= alpha; w.w *= alpha; }
                 const float wt[4] = {w.x, w.y, w.z, w.w};
+                // whole blocks, no per-step test: padding entries carry w = 0 and point at the zero row
+                // (measured: skipping the padded steps with predicated loads bought nothing)
 #pragma unroll
                 for (int t = 0; t < 4; ++t) {
-                    if (it + t < nit) {
-                        const float *xr = xst + ((r4 >> (8 * t)) & 255u) * MT;
+                    const uint8_t *xr = xst + __byte_perm(r4, 0u, 0x4440u + t) * (MT * 4);
 #pragma unroll
-                        for (int f = 0; f < NF4; ++f) {
-                            const float4 xv = *reinterpret_cast<const float4 *>(xr + 32 * f);
-                            acc[rr][f].x = fmaf(wt[t], xv.x, acc[rr][f].x);
-                            acc[rr][f].y = fmaf(wt[t], xv.y, acc[rr][f].y);
-                            acc[rr][f].z = fmaf(wt[t], xv.z, acc[rr][f].z);
-                            acc[rr][f].w = fmaf(wt[t], xv.w, acc[rr][f].w);
-                        }
+                    for (int f = 0; f < NF4; ++f) {
+                        const float4 xv = *reinterpret_cast<const float4 *>(xr + 128 * f);
+                        acc[rr][f].x = fmaf(wt[t], xv.x, acc[rr][f].x);
+                        acc[rr][f].y = fmaf(wt[t], xv.y, acc[rr][f].y);
+                        acc[rr][f].z = fmaf(wt[t], xv.z, acc[rr][f].z);
+                        acc[rr][f].w = fmaf(wt[t], xv.w, acc[rr][f].w);
                     }
                 }
             }
@@ -217,7 +269,7 @@ template <int NWARPS, int NF4, int STAGES>
 static int launch_tile(sblas_b200_matrix *mat, const float *xt, int k_alloc, float *d_c, int ldc, int m, float alpha,
                        float beta, cudaStream_t stream) {
     constexpr int MT = 32 * NF4;
-    const size_t smem = (size_t)STAGES * 256 * MT * 4 + STAGES * 8;
+    const size_t smem = (size_t)STAGES * 256 * MT * 4 + (size_t)NWARPS * kRingBytes + (STAGES + 2 * NWARPS) * 8;
     static bool configured = false;                              // per template instance
     if (!configured) {
         SB_CUDA(cudaFuncSetAttribute(spmm_tile_kernel<NWARPS, NF4, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -235,10 +287,13 @@ static int launch_tile(sblas_b200_matrix *mat, const float *xt, int k_alloc, flo
 // Variant selection: "<warps><f4>" from SBLAS_B200_TILE (experiments), else by shape.
 int run_spmm_tile(sblas_b200_matrix *mat, const float *d_a, int m, int lda, float *d_c, int ldc, float alpha,
                   float beta, cudaStream_t stream) {
-    int nwarps = 8, nf4 = (m > 32) ? 2 : 1;
-    if (const char *env = getenv("SBLAS_B200_TILE")) {
-        if (env[0] == '4' || env[0] == '8') nwarps = env[0] - '0';
-        if (env[1] == '1' || env[1] == '2') nf4 = env[1] - '0';
+    // two float4 per lane halve the per-entry bookkeeping, but only when that still leaves a full grid
+    int nwarps = 16, nf4 = 1;
+    if (m > 32 && (int64_t)((mat->tile_ngroups + 15) / 16) * ((m + 63) / 64) >= 140) nf4 = 2;
+    if (const char *env = getenv("SBLAS_B200_TILE")) {          // "<warps: 8|g(16)><float4s per lane: 1|2>"
+        if (env[0] == '8') nwarps = 8;
+        if (env[0] == 'g') nwarps = 16;
+        if (env[0] && (env[1] == '1' || env[1] == '2')) nf4 = env[1] - '0';
     }
     const int MT = 32 * nf4;
     const int ntiles = (m + MT - 1) / MT;
@@ -257,8 +312,8 @@ int run_spmm_tile(sblas_b200_matrix *mat, const float *d_a, int m, int lda, floa
     } timer(mat, stream);
     if (nwarps == 8 && nf4 == 2) return launch_tile<8, 2, 2>(mat, mat->d_ws, k_alloc, d_c, ldc, m, alpha, beta, stream);
     if (nwarps == 8 && nf4 == 1) return launch_tile<8, 1, 3>(mat, mat->d_ws, k_alloc, d_c, ldc, m, alpha, beta, stream);
-    if (nwarps == 4 && nf4 == 2) return launch_tile<4, 2, 2>(mat, mat->d_ws, k_alloc, d_c, ldc, m, alpha, beta, stream);
-    return launch_tile<4, 1, 3>(mat, mat->d_ws, k_alloc, d_c, ldc, m, alpha, beta, stream);
+    if (nwarps == 16 && nf4 == 2) return launch_tile<16, 2, 2>(mat, mat->d_ws, k_alloc, d_c, ldc, m, alpha, beta, stream);
+    return launch_tile<16, 1, 3>(mat, mat->d_ws, k_alloc, d_c, ldc, m, alpha, beta, stream);
 }
 
 }  // namespace sblas_b200

@@ -7,15 +7,15 @@
 // reads its X row from shared memory.  That needs, per (W row, chunk), the entries of that row
 // whose column falls in the chunk -- a contiguous piece of the CSR row, since columns ascend.
 //
-// Layout ("blocks"): W rows are taken in groups of kTileRows = 16, X rows in chunks of
-// kTileK = 255.  For each (group, chunk), the pieces of the 16 rows follow one another, each
+// Layout ("blocks"): W rows are taken in groups of kTileRows = 8, X rows in chunks of
+// kTileK = 255.  For each (group, chunk), the pieces of the 8 rows follow one another, each
 // padded to whole blocks of 16 entries.  A block is 80 bytes:
 //     float  w[4][4]   w[s][t] = table[code] of entry 4*t + s      (s = warp slot, t = step)
 //     uint8  r[4][4]   r[s][t] = column - 255*chunk of that entry  (255 = the zero row, padding)
 // so that one 128-bit load gives a slot its four next weights and one 32-bit load its four
 // next X-row offsets.  Padding entries are (w = 0, r = 255): they multiply an all-zero row of
 // shared memory and so never touch real X data.
-// grp_ptr[group*nchunks + chunk] = first block of the run; seg_len[(group*nchunks + chunk)*16 + row]
+// grp_ptr[group*nchunks + chunk] = first block of the run; seg_len[(group*nchunks + chunk)*8 + row]
 // = number of real entries of that row in the chunk.
 #include <stdlib.h>
 

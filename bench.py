@@ -313,6 +313,22 @@ def run_ours(args):
         e2e_s += time.perf_counter() - t0
     checksum = float(h_c.sum())
 
+    # optional reassembly of Y on every rank (not part of `value`: the path itself has no collective)
+    gather_ms = None
+    if world > 1:
+        from sparsematrix_b200 import sharding
+        splits = [r * n for r in range(world + 1)]
+        for _ in range(2):
+            sharding.gather_output(d_c, m, splits)
+        barrier()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record(stream)
+        for _ in range(5):
+            sharding.gather_output(d_c, m, splits)
+        g1.record(stream)
+        barrier()
+        gather_ms = g0.elapsed_time(g1) / 5
+
     t = torch.tensor([total_ms, warm_ms, e2e_s * 1e3, kern_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -348,6 +364,14 @@ def run_ours(args):
                     "api": "sblas_b200_addmatmat_host (pinned host A, C; synchronous)", "checksum": checksum},
             "gpu_launches": int(launches), "clocks": clocks.summary(),
         }
+        traffic_file = os.path.join(ROOT, "profiles", "traffic.json")     # dram bytes/launch from the ncu --set full capture
+        if os.path.exists(traffic_file):
+            tr = json.load(open(traffic_file)).get(args.workload)
+            if tr:
+                line["roofline"]["traffic"] = tr["dram_bytes_per_launch"]
+                line["roofline"]["traffic_source"] = tr["source"]
+        if gather_ms is not None:
+            line["reassembly_allgather_ms"] = gather_ms
         if args.cpu_baseline and world >= 1:
             ref = CpuReference(inp)
             ref.call()

@@ -26,6 +26,9 @@ namespace sblas_b200 {
 __device__ __forceinline__ int4 ld_stream_int4(const int4 *p) { return __ldcs(p); }
 __device__ __forceinline__ uint32_t ld_stream_u32(const uint32_t *p) { return __ldcs(p); }
 
+// x gather: through L1 (ld.global.nc) or L2-only (ld.global.cg); chosen per launch (uniform)
+__device__ __forceinline__ float ld_x(const float *p, int cg) { return cg ? __ldcg(p) : __ldg(p); }
+
 // ---- K-scale: C *= beta (alpha == 0 path; sparse-matrix.cc:149-152) ----------------------
 __global__ void __launch_bounds__(256)
 scale_kernel(float *__restrict__ c, int m, int n, int ldc, float beta) {
@@ -44,7 +47,7 @@ __global__ void __launch_bounds__(256)
 spmv_rows_kernel(const int32_t *__restrict__ row_ptr, const int4 *__restrict__ col4,
                  const uint32_t *__restrict__ code4, const float *__restrict__ table, int T,
                  const float *__restrict__ x, float *__restrict__ y, int n, float alpha, float beta,
-                 int long_threshold) {
+                 int long_threshold, int xcg) {
     __shared__ float s_tab[256];
     s_tab[threadIdx.x] = (threadIdx.x < T) ? table[threadIdx.x] * alpha : 0.0f;    // val_table[code]*alpha
     __syncthreads();
@@ -62,16 +65,16 @@ spmv_rows_kernel(const int32_t *__restrict__ row_ptr, const int4 *__restrict__ c
             const uint32_t cd = ld_stream_u32(code4 + b);
             const int base = b << 2;
             if (base >= s && base + 3 < e) {            // interior block: four independent gathers
-                const float x0 = __ldg(x + c.x), x1 = __ldg(x + c.y), x2 = __ldg(x + c.z), x3 = __ldg(x + c.w);
+                const float x0 = ld_x(x + c.x, xcg), x1 = ld_x(x + c.y, xcg), x2 = ld_x(x + c.z, xcg), x3 = ld_x(x + c.w, xcg);
                 acc = fmaf(x0, s_tab[cd & 255u], acc);
                 acc = fmaf(x1, s_tab[(cd >> 8) & 255u], acc);
                 acc = fmaf(x2, s_tab[(cd >> 16) & 255u], acc);
                 acc = fmaf(x3, s_tab[cd >> 24], acc);
             } else {                                    // first / last block of the row
-                if (base + 0 >= s && base + 0 < e) acc = fmaf(__ldg(x + c.x), s_tab[cd & 255u], acc);
-                if (base + 1 >= s && base + 1 < e) acc = fmaf(__ldg(x + c.y), s_tab[(cd >> 8) & 255u], acc);
-                if (base + 2 >= s && base + 2 < e) acc = fmaf(__ldg(x + c.z), s_tab[(cd >> 16) & 255u], acc);
-                if (base + 3 >= s && base + 3 < e) acc = fmaf(__ldg(x + c.w), s_tab[cd >> 24], acc);
+                if (base + 0 >= s && base + 0 < e) acc = fmaf(ld_x(x + c.x, xcg), s_tab[cd & 255u], acc);
+                if (base + 1 >= s && base + 1 < e) acc = fmaf(ld_x(x + c.y, xcg), s_tab[(cd >> 8) & 255u], acc);
+                if (base + 2 >= s && base + 2 < e) acc = fmaf(ld_x(x + c.z, xcg), s_tab[(cd >> 16) & 255u], acc);
+                if (base + 3 >= s && base + 3 < e) acc = fmaf(ld_x(x + c.w, xcg), s_tab[cd >> 24], acc);
             }
         }
     }
@@ -90,7 +93,7 @@ __global__ void __launch_bounds__(256)
 spmv_long_segment_kernel(const int32_t *__restrict__ seg_begin, const int32_t *__restrict__ seg_end,
                          const int4 *__restrict__ col4, const uint32_t *__restrict__ code4,
                          const float *__restrict__ table, int T, const float *__restrict__ x, float alpha,
-                         float *__restrict__ partial) {
+                         float *__restrict__ partial, int xcg) {
     __shared__ float s_tab[256];
     __shared__ float s_red[8];
     s_tab[threadIdx.x] = (threadIdx.x < T) ? table[threadIdx.x] * alpha : 0.0f;
@@ -102,10 +105,10 @@ spmv_long_segment_kernel(const int32_t *__restrict__ seg_begin, const int32_t *_
         const int4 c = ld_stream_int4(col4 + b);
         const uint32_t cd = ld_stream_u32(code4 + b);
         const int base = b << 2;
-        if (base + 0 >= s && base + 0 < e) acc = fmaf(__ldg(x + c.x), s_tab[cd & 255u], acc);
-        if (base + 1 >= s && base + 1 < e) acc = fmaf(__ldg(x + c.y), s_tab[(cd >> 8) & 255u], acc);
-        if (base + 2 >= s && base + 2 < e) acc = fmaf(__ldg(x + c.z), s_tab[(cd >> 16) & 255u], acc);
-        if (base + 3 >= s && base + 3 < e) acc = fmaf(__ldg(x + c.w), s_tab[cd >> 24], acc);
+        if (base + 0 >= s && base + 0 < e) acc = fmaf(ld_x(x + c.x, xcg), s_tab[cd & 255u], acc);
+        if (base + 1 >= s && base + 1 < e) acc = fmaf(ld_x(x + c.y, xcg), s_tab[(cd >> 8) & 255u], acc);
+        if (base + 2 >= s && base + 2 < e) acc = fmaf(ld_x(x + c.z, xcg), s_tab[(cd >> 16) & 255u], acc);
+        if (base + 3 >= s && base + 3 < e) acc = fmaf(ld_x(x + c.w, xcg), s_tab[cd >> 24], acc);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
@@ -263,6 +266,15 @@ private:
     cudaEvent_t a_ = nullptr, b_ = nullptr;
 };
 
+static int x_load_mode() {
+    static int mode = -1;
+    if (mode < 0) {
+        const char *env = getenv("SBLAS_B200_XLOAD");
+        mode = (env && env[0] == 'c') ? 1 : 0;
+    }
+    return mode;
+}
+
 template <int LPR>
 static void launch_spmv_rows(const sblas_b200_matrix *mat, const float *x, float *y, float alpha, float beta,
                              cudaStream_t stream) {
@@ -270,7 +282,7 @@ static void launch_spmv_rows(const sblas_b200_matrix *mat, const float *x, float
     const unsigned grid = (unsigned)((threads + 255) / 256);
     SB_LAUNCH(spmv_rows_kernel<LPR>, grid, 256, 0, stream, mat->d_row_ptr, reinterpret_cast<const int4 *>(mat->d_col),
               reinterpret_cast<const uint32_t *>(mat->d_code), mat->d_table, mat->T, x, y, mat->n, alpha, beta,
-              mat->long_threshold);
+              mat->long_threshold, x_load_mode());
 }
 
 static int run_spmv(sblas_b200_matrix *mat, const float *x, float *y, float alpha, float beta, cudaStream_t stream) {
@@ -291,7 +303,7 @@ static int run_spmv(sblas_b200_matrix *mat, const float *x, float *y, float alph
         if (rc != SBLAS_B200_OK) return rc;
         SB_LAUNCH(spmv_long_segment_kernel, mat->n_long_seg, 256, 0, stream, mat->d_seg_begin, mat->d_seg_end,
                   reinterpret_cast<const int4 *>(mat->d_col), reinterpret_cast<const uint32_t *>(mat->d_code),
-                  mat->d_table, mat->T, x, alpha, mat->d_partial);
+                  mat->d_table, mat->T, x, alpha, mat->d_partial, x_load_mode());
         SB_LAUNCH(spmv_long_finish_kernel, (mat->n_long + 127) / 128, 128, 0, stream, mat->d_long_rows,
                   mat->d_long_seg_ptr, mat->d_partial, y, beta, mat->n_long);
         SB_CHECK_LAUNCH();

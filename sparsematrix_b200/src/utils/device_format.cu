@@ -300,8 +300,10 @@ int plan_spmv(sblas_b200_matrix *mat, const int32_t *h_row_ptr) {
     }
     mat->max_row_nnz = max_len;
     const double mean = nonempty ? (double)mat->nnz / (double)nonempty : 0.0;
-    // each lane consumes one aligned block of 4 non-zeros per iteration: aim at ~1 iteration for a typical row
-    int lanes = next_pow2((int)((mean + 3.0) / 4.0));
+    // each lane consumes one aligned block of 4 non-zeros per iteration: aim at ~2 iterations for a typical row
+    // measured on config 4 (mean 16): 2 lanes beat 4 and 8 -- the row kernel is bound by the L1TEX
+    // rate of the scattered x gathers, and fewer lanes per row mean fewer idle lanes on short rows
+    int lanes = next_pow2((int)((mean + 7.0) / 8.0));
     lanes = std::min(32, std::max(2, lanes));
     if (const char *env = getenv("SBLAS_B200_SPMV_LANES")) {
         const int v = atoi(env);

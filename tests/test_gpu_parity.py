@@ -284,3 +284,16 @@ def test_virtual_shards_concatenate_to_unsharded_result(parts):
             assert np.max(np.abs(pieces - whole)) <= 1e-5 * np.max(np.abs(whole))
         else:
             assert_bits_equal(pieces, whole, f"virtual shards parts={parts} m={m}")
+
+
+# ------------------------------------------------------------------ the C++ harness (src/test), same library
+@pytest.mark.parametrize("binary,expect", [("sparse-matrix_test", "SparseMatrix Test success"),
+                                           ("parity_test", "Parity Test success")])
+def test_cpp_harness_binaries(binary, expect):
+    import os
+    import subprocess
+    path = os.path.join(os.path.dirname(sb.LIB_PATH), "..", "bin", binary)
+    if not os.path.exists(path):
+        pytest.skip(f"{binary} not built")
+    out = subprocess.run([path], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and expect in out.stdout, out.stdout[-2000:] + out.stderr[-500:]

@@ -97,12 +97,12 @@ struct sblas_b200_matrix {
 
     // SpMM tile format (src/utils/tile_format.cu), built on the first large-m product.
     // Row groups of 8 W rows x chunks of 255 X rows; per (group, chunk) a contiguous run of
-    // 80-byte blocks: 16 fp32 weights (slot-major) + 16 one-byte X-row offsets inside the chunk.
+    // 80-byte quad rows: per warp slot 4 fp32 weights + 4 one-byte X-row offsets inside the chunk.
     int tile_state = 0;                 // 0 = not built yet, 1 = built, -1 = not worthwhile / not possible
     bool csr_sorted = true;             // columns ascending inside every row (required by the tile build)
-    uint8_t *d_tile_blocks = nullptr;   // [tile_nblocks + 2][80]
+    uint8_t *d_tile_blocks = nullptr;   // [tile_nblocks + 2][80] quad rows
     int32_t *d_grp_ptr = nullptr;       // [tile_ngroups * tile_nchunks + 1] first block of each (group, chunk)
-    uint16_t *d_seg_len = nullptr;      // [tile_ngroups * tile_nchunks * 8] entries of each (row, chunk)
+    uint32_t *d_grp_nq = nullptr;       // [tile_ngroups * tile_nchunks] quad rows of row pair 0 | pair 1 << 16
     int32_t tile_ngroups = 0, tile_nchunks = 0;
     int64_t tile_nblocks = 0;
 
@@ -119,7 +119,6 @@ int exclusive_scan_i32(const int32_t *d_in, int n, int32_t *d_out, cudaStream_t 
 // src/utils/tile_format.cu
 constexpr int kTileRows = 8;         // W rows per group = one warp's share of a CTA's row block
 constexpr int kTileK = 255;          // X rows per chunk; offset 255 addresses an all-zero row (padding entries)
-constexpr int kBlockEntries = 16;
 constexpr int kBlockBytes = 80;
 int build_tile_format(sblas_b200_matrix *mat, cudaStream_t stream);
 // src/sparse/spmm_tile.cu

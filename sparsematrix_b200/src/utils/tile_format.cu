@@ -7,16 +7,19 @@
 // reads its X row from shared memory.  That needs, per (W row, chunk), the entries of that row
 // whose column falls in the chunk -- a contiguous piece of the CSR row, since columns ascend.
 //
-// Layout ("blocks"): W rows are taken in groups of kTileRows = 8, X rows in chunks of
-// kTileK = 255.  For each (group, chunk), the pieces of the 8 rows follow one another, each
-// padded to whole blocks of 16 entries.  A block is 80 bytes:
-//     float  w[4][4]   w[s][t] = table[code] of entry 4*t + s      (s = warp slot, t = step)
-//     uint8  r[4][4]   r[s][t] = column - 255*chunk of that entry  (255 = the zero row, padding)
-// so that one 128-bit load gives a slot its four next weights and one 32-bit load its four
-// next X-row offsets.  Padding entries are (w = 0, r = 255): they multiply an all-zero row of
-// shared memory and so never touch real X data.
-// grp_ptr[group*nchunks + chunk] = first block of the run; seg_len[(group*nchunks + chunk)*8 + row]
-// = number of real entries of that row in the chunk.
+// Layout ("quad rows"): W rows are taken in groups of kTileRows = 8 (one warp), X rows in chunks
+// of kTileK = 255.  A warp is 4 slots of 8 lanes; slot s owns the two rows 8g + s and 8g + 4 + s
+// of its group and walks each of them on its own, in column order (the reference's accumulation
+// order, kernel.cc:780-796).  One quad row is what the warp consumes in four steps: for every
+// slot the next four entries of that slot's current row.  80 bytes:
+//     float  w[4][4]   w[s][t] = table[code] of the slot's entry t      (one 128-bit load per slot)
+//     uint8  r[4][4]   r[s][t] = column - 255*chunk of that entry, or 255 = "no entry" (skipped)
+// For (group, chunk) the quad rows of row pair 0 (rows 8g+0..3) come first, then those of row
+// pair 1 (rows 8g+4..7); each pair takes as many quad rows as its longest piece needs, shorter
+// pieces are filled with "no entry" -- those lanes are predicated off in the kernel and cost
+// no shared-memory bandwidth.
+// grp_ptr[group*nchunks + chunk] = first quad row of the run;
+// grp_nq[group*nchunks + chunk]  = quad rows of pair 0 | quad rows of pair 1 << 16.
 #include <stdlib.h>
 
 #include <algorithm>
@@ -34,60 +37,73 @@ __device__ __forceinline__ int lower_bound_col(const int32_t *__restrict__ col, 
     return lo;
 }
 
-// thread per (group, chunk, row-in-group): entries of that row inside the chunk; blocks per (group, chunk)
+// thread per (group, chunk, row-in-group); the 8 threads of one (group, chunk) are neighbours in a warp
 __global__ void __launch_bounds__(256)
 tile_count_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col, int n, int nchunks,
-                  int64_t total, uint16_t *__restrict__ seg_len, int32_t *__restrict__ grp_blocks) {
+                  int64_t total, uint32_t *__restrict__ grp_nq, int32_t *__restrict__ grp_blocks) {
     const int64_t idx = blockIdx.x * (int64_t)256 + threadIdx.x;
-    if (idx >= total) return;
+    const bool in = idx < total;
     const int jj = (int)(idx % kTileRows);
     const int64_t gc = idx / kTileRows;
-    const int c = (int)(gc % nchunks), g = (int)(gc / nchunks);
-    const int j = g * kTileRows + jj;
-    int len = 0;
-    if (j < n) {
-        const int s = row_ptr[j], e = row_ptr[j + 1];
-        const int lo = lower_bound_col(col, s, e, c * kTileK);
-        const int hi = lower_bound_col(col, lo, e, (c + 1) * kTileK);
-        len = hi - lo;
+    int quads = 0;
+    if (in) {
+        const int c = (int)(gc % nchunks), g = (int)(gc / nchunks);
+        const int j = g * kTileRows + jj;
+        if (j < n) {
+            const int s = row_ptr[j], e = row_ptr[j + 1];
+            const int lo = lower_bound_col(col, s, e, c * kTileK);
+            const int hi = lower_bound_col(col, lo, e, (c + 1) * kTileK);
+            quads = (hi - lo + 3) >> 2;
+        }
     }
-    seg_len[idx] = (uint16_t)len;
-    if (len) atomicAdd(&grp_blocks[gc], (len + kBlockEntries - 1) / kBlockEntries);
+    // longest piece of the row pair: rows jj = 4*pair + slot
+    quads = max(quads, __shfl_xor_sync(0xffffffffu, quads, 1));
+    quads = max(quads, __shfl_xor_sync(0xffffffffu, quads, 2));
+    const int other = __shfl_xor_sync(0xffffffffu, quads, 4);
+    if (in && jj == 0) {
+        grp_nq[gc] = (uint32_t)quads | ((uint32_t)other << 16);
+        grp_blocks[gc] = quads + other;
+    }
 }
 
-// thread per (group, chunk, row-in-group): write that row's blocks
+// thread per (group, chunk, row-in-group): write that row's share of the quad rows
 __global__ void __launch_bounds__(256)
 tile_fill_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
                  const uint8_t *__restrict__ code, const float *__restrict__ table, int n, int nchunks,
-                 int64_t total, const uint16_t *__restrict__ seg_len, const int32_t *__restrict__ grp_ptr,
+                 int64_t total, const uint32_t *__restrict__ grp_nq, const int32_t *__restrict__ grp_ptr,
                  uint8_t *__restrict__ blocks) {
     const int64_t idx = blockIdx.x * (int64_t)256 + threadIdx.x;
     if (idx >= total) return;
     const int jj = (int)(idx % kTileRows);
     const int64_t gc = idx / kTileRows;
-    const int len = seg_len[idx];
-    if (len == 0) return;
+    const uint32_t nq2 = grp_nq[gc];
+    const int pair = jj >> 2, slot = jj & 3;
+    const int nq = pair ? (int)(nq2 >> 16) : (int)(nq2 & 0xffffu);
+    if (nq == 0) return;
     const int c = (int)(gc % nchunks), g = (int)(gc / nchunks);
     const int j = g * kTileRows + jj;
-    int64_t blk = grp_ptr[gc];
-    for (int q = 0; q < jj; ++q) blk += (seg_len[gc * kTileRows + q] + kBlockEntries - 1) / kBlockEntries;
-    const int lo = lower_bound_col(col, row_ptr[j], row_ptr[j + 1], c * kTileK);
-    const int nblk = (len + kBlockEntries - 1) / kBlockEntries;
-    for (int b = 0; b < nblk; ++b) {
-        float *w = reinterpret_cast<float *>(blocks + (blk + b) * kBlockBytes);
-        uint8_t *r = blocks + (blk + b) * kBlockBytes + 64;
-        for (int q = 0; q < kBlockEntries; ++q) {
-            const int e = b * kBlockEntries + q;          // entry 4*t + s  ->  w[s][t]
-            const int s = q & 3, t = q >> 2;
-            float wv = 0.0f;
-            int rv = kTileK;                              // the zero row
+    int lo = 0, len = 0;
+    if (j < n) {
+        const int s = row_ptr[j], e = row_ptr[j + 1];
+        lo = lower_bound_col(col, s, e, c * kTileK);
+        len = lower_bound_col(col, lo, e, (c + 1) * kTileK) - lo;
+    }
+    const int64_t first = (int64_t)grp_ptr[gc] + (pair ? (int)(nq2 & 0xffffu) : 0);
+    for (int q = 0; q < nq; ++q) {
+        uint8_t *blk = blocks + (first + q) * kBlockBytes;
+        float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+        uint32_t r4 = 0xffffffffu;                       // four times "no entry"
+        float *wp = &w.x;
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            const int e = 4 * q + t;
             if (e < len) {
-                wv = table[code[lo + e]];
-                rv = col[lo + e] - c * kTileK;
+                wp[t] = table[code[lo + e]];
+                r4 = (r4 & ~(0xffu << (8 * t))) | ((uint32_t)(col[lo + e] - c * kTileK) << (8 * t));
             }
-            w[s * 4 + t] = wv;
-            r[s * 4 + t] = (uint8_t)rv;
         }
+        *reinterpret_cast<float4 *>(blk + slot * 16) = w;
+        *reinterpret_cast<uint32_t *>(blk + 64 + slot * 4) = r4;
     }
 }
 
@@ -105,14 +121,14 @@ int build_tile_format(sblas_b200_matrix *mat, cudaStream_t stream) {
     if (const char *env = getenv("SBLAS_B200_NO_TILE")) { if (env[0] == '1') return SBLAS_B200_OK; }
     const int64_t total = ngc * kTileRows;
     int32_t *d_grp_blocks = nullptr;
-    SB_CUDA(cudaMalloc((void **)&mat->d_seg_len, (size_t)total * 2));
+    SB_CUDA(cudaMalloc((void **)&mat->d_grp_nq, (size_t)ngc * 4));
     SB_CUDA(cudaMalloc((void **)&mat->d_grp_ptr, ((size_t)ngc + 1) * 4));
     SB_CUDA(cudaMalloc((void **)&d_grp_blocks, ((size_t)ngc + 1) * 4));
     cudaError_t e = cudaMemsetAsync(d_grp_blocks, 0, ((size_t)ngc + 1) * 4, stream);
     const unsigned grid = (unsigned)((total + 255) / 256);
     if (e == cudaSuccess) {
         SB_LAUNCH(tile_count_kernel, grid, 256, 0, stream, mat->d_row_ptr, mat->d_col, mat->n, nchunks, total,
-                  mat->d_seg_len, d_grp_blocks);
+                  mat->d_grp_nq, d_grp_blocks);
         exclusive_scan_i32(d_grp_blocks, (int)ngc, mat->d_grp_ptr, stream);
     }
     int32_t nblocks = 0;
@@ -120,18 +136,18 @@ int build_tile_format(sblas_b200_matrix *mat, cudaStream_t stream) {
     if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
     cudaFree(d_grp_blocks);
     if (e != cudaSuccess) return cuda_fail(e, "tile format count", __FILE__, __LINE__);
-    // +2 blocks: the kernel's look-ahead loads run two blocks past the last real one
+    // +2 quad rows: the kernel's look-ahead loads run past the last real one
     const size_t bytes = ((size_t)nblocks + 2) * kBlockBytes;
     SB_CUDA(cudaMalloc((void **)&mat->d_tile_blocks, bytes));
-    SB_CUDA(cudaMemsetAsync(mat->d_tile_blocks + (size_t)nblocks * kBlockBytes, 0, 2 * kBlockBytes, stream));
+    SB_CUDA(cudaMemsetAsync(mat->d_tile_blocks + (size_t)nblocks * kBlockBytes, 0xff, 2 * kBlockBytes, stream));
     SB_LAUNCH(tile_fill_kernel, grid, 256, 0, stream, mat->d_row_ptr, mat->d_col, mat->d_code, mat->d_table, mat->n,
-              nchunks, total, mat->d_seg_len, mat->d_grp_ptr, mat->d_tile_blocks);
+              nchunks, total, mat->d_grp_nq, mat->d_grp_ptr, mat->d_tile_blocks);
     SB_CHECK_LAUNCH();
     SB_CUDA(cudaStreamSynchronize(stream));
     mat->tile_ngroups = ngroups;
     mat->tile_nchunks = nchunks;
     mat->tile_nblocks = nblocks;
-    mat->format_bytes += (int64_t)bytes + total * 2 + (ngc + 1) * 4;
+    mat->format_bytes += (int64_t)bytes + ngc * 4 + (ngc + 1) * 4;
     mat->tile_state = 1;
     return SBLAS_B200_OK;
 }

@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libsblas_b200.so")
+LIB_PATH = os.environ.get("SBLAS_B200_LIB") or os.path.join(_HERE, "lib", "libsblas_b200.so")   # override: kernel experiments only
 
 OK, EINVAL, ECUDA, ENOMEM, EFORMAT = 0, -1, -2, -3, -4
 

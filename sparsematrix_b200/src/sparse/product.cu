@@ -325,11 +325,8 @@ static int run_spmm(sblas_b200_matrix *mat, const float *d_a, int m, int lda, fl
     int tile_min_m = 17;
     if (const char *env = getenv("SBLAS_B200_TILE_MIN_M")) tile_min_m = atoi(env);
     if (m >= tile_min_m) {
-        if (mat->tile_state == 0) {
-            const int brc = build_tile_format(mat, stream);
-            if (brc != SBLAS_B200_OK) return brc;
-        }
-        if (mat->tile_state == 1) return run_spmm_tile(mat, d_a, m, lda, d_c, ldc, alpha, beta, stream);
+        const int trc = run_spmm_tile(mat, d_a, m, lda, d_c, ldc, alpha, beta, stream);
+        if (trc <= 0) return trc;                       // done (0) or failed (< 0); 1 = no tile layout, use the gather kernel
     }
     const int mp = (m + 3) & ~3;
     int rc = ensure_buffer(&mat->d_ws, &mat->ws_bytes, (size_t)mat->k * mp * 4);

@@ -18,9 +18,9 @@
 // with the roles of "contiguous m" kept: the m dense values of one X row are contiguous in shared
 // memory exactly like aa[] is contiguous there.
 //
-// The warp's entries for all chunks form one contiguous stream of 80-byte quad rows, which also
-// arrives by bulk copies, into a private two-half ring in shared memory (a warp's entry fetch would
-// otherwise sit on the L2/HBM latency).
+// The warp's entries for all chunks form one contiguous stream of 80-byte quad rows, which the
+// warp copies into a private ring in shared memory with cp.async, three segments of 8 quad rows
+// ahead of use (a warp's entry fetch would otherwise sit on the L2/HBM latency).
 //
 // Accumulators stay in registers across the whole k loop (2 rows x NF4 float4 per lane); the result
 // tile goes through shared memory so that C (row-major m x n = Y^T) is written in 128-byte rows --
@@ -69,25 +69,24 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
     bulk_g2s_addr(smem_u32(dst), src, bytes, bar);
 }
 
-constexpr int kRingHalf = 32;                                   // quad rows per half of a warp's ring
-constexpr int kRingBytes = 2 * kRingHalf * kBlockBytes;        // 5120 B per warp
-constexpr int kMaxWarps = 16;                                   // consumer warps per CTA
+constexpr int kMaxRows = 128;                                   // W rows per CTA at most
 
-// The warp has just read the last quad row of a ring half (`consumed` read so far): refill that
-// half with the quad rows one ring ahead, then make sure the half it moves into has landed.
-__device__ __noinline__ void ring_turn(uint32_t ring, uint64_t *wbar, const uint8_t *stream, int consumed, int total,
-                                       int lane) {
-    const int done_half = ((consumed - 1) / kRingHalf) & 1;
-    __syncwarp();
-    const int nxt = consumed + kRingHalf;                        // first quad row of the refill
-    if (lane == 0 && nxt < total) {
-        const int cnt = min(kRingHalf, total - nxt);
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        mbar_expect_tx(&wbar[done_half], (uint32_t)cnt * kBlockBytes);
-        bulk_g2s_addr(ring + done_half * kRingHalf * kBlockBytes, stream + (size_t)nxt * kBlockBytes,
-                      (uint32_t)cnt * kBlockBytes, &wbar[done_half]);
-    }
-    if (consumed < total) mbar_wait(&wbar[done_half ^ 1], (uint32_t)((consumed / (2 * kRingHalf)) & 1));
+// The warp's quad-row stream goes through a private ring of kRingSegs segments of kSegRows quad rows;
+// a segment is fetched by the warp itself with 16-byte cp.async (LDGSTS) three segments ahead.
+constexpr int kSegRows = 8, kRingSegs = 4;
+constexpr int kSegBytes = kSegRows * kBlockBytes;                // 640
+constexpr int kRingBytes = kRingSegs * kSegBytes;                // 2560 B per warp
+
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void *src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+// fetch segment `seg` of the stream into its ring position; always one commit group
+__device__ __forceinline__ void fetch_segment(uint32_t ring, const uint8_t *stream, int seg, int lane) {
+    const uint8_t *src = stream + (size_t)seg * kSegBytes + lane * 16;
+    const uint32_t dst = ring + (seg & (kRingSegs - 1)) * kSegBytes + lane * 16;
+    cp_async16(dst, src);
+    if (lane < (kSegBytes - 512) / 16) cp_async16(dst + 512, src + 512);
+    asm volatile("cp.async.commit_group;" ::: "memory");
 }
 
 // One entry of this lane's slot: acc[0..NF4) += w * X[off][float4 lanes], skipped when off == 255.
@@ -103,11 +102,15 @@ __device__ __forceinline__ void slot_step(float4 (&acc)[NF4], float4 (&x)[NF4], 
             ".reg .u32 a;\n"
             "setp.ne.u32 p, %8, 255;\n"
             "mad.lo.u32 a, %8, %9, %10;\n"
+#ifndef EXP_NOLDS
             "@p ld.shared.v4.f32 {%4, %5, %6, %7}, [a];\n"
+#endif
             "@p fma.rn.f32 %0, %11, %4, %0;\n"
+#ifndef EXP_NOFMA
             "@p fma.rn.f32 %1, %11, %5, %1;\n"
             "@p fma.rn.f32 %2, %11, %6, %2;\n"
             "@p fma.rn.f32 %3, %11, %7, %3;\n"
+#endif
             "}\n"
             : "+f"(acc[0].x), "+f"(acc[0].y), "+f"(acc[0].z), "+f"(acc[0].w), "+f"(x[0].x), "+f"(x[0].y), "+f"(x[0].z),
               "+f"(x[0].w)
@@ -160,43 +163,60 @@ transpose_in_tiled_kernel(const float *__restrict__ a, int m, int k, int lda, fl
     }
 }
 
+
 // blockDim.x = (nwarps + 1) * 32: nwarps consumer warps and one producer warp (the last).
-template <int NF4, int STAGES, bool SCALE>
-__global__ void __maxnreg__(112)
+// RS = W rows per slot (a warp owns 4*RS rows).
+template <int RS, int NF4, int STAGES, bool SCALE>
+__global__ void __maxnreg__((RS == 1 && NF4 == 1) ? 64 : 112)
 spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__ grp_ptr,
                  const uint32_t *__restrict__ grp_nq, const int32_t *__restrict__ row_ptr, int ngroups, int nchunks,
                  int n, const float *__restrict__ xt, int k_alloc, float *__restrict__ c, int ldc, int m, float alpha,
                  float beta, int nwarps) {
-    constexpr int MT = 32 * NF4;
+    constexpr int MT = 32 * NF4, G = 4 * RS;
     constexpr int STAGE_BYTES = 256 * MT * 4;                    // 255 data rows, padded to a round size
     constexpr uint32_t CHUNK_BYTES = kTileK * MT * 4;
     extern __shared__ __align__(128) uint8_t smem_raw[];
     uint8_t *ring_base = smem_raw + (size_t)STAGES * STAGE_BYTES;                           // [nwarps][kRingBytes]
     uint64_t *full = reinterpret_cast<uint64_t *>(ring_base + (size_t)nwarps * kRingBytes);  // [STAGES]
     uint64_t *empty = full + STAGES;                                                         // [STAGES]
-    uint64_t *wfull = empty + STAGES;                                                        // [nwarps][2]
-    __shared__ int s_len[kMaxWarps * kTileRows];
+    uint32_t *s_nq = reinterpret_cast<uint32_t *>(empty + STAGES);                           // [nwarps][nchunks]
+    __shared__ int s_len[kMaxRows];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int slot = lane >> 3, c8 = lane & 7;
-    const int RB = nwarps * kTileRows;
+    const int RB = nwarps * G;
     const int j0 = blockIdx.x * RB;
+    const int m0 = blockIdx.y * MT;
     const float *xt_tile = xt + (size_t)blockIdx.y * k_alloc * MT;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], nwarps); }
-        for (int s = 0; s < 2 * nwarps; ++s) mbar_init(&wfull[s], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    for (int i = threadIdx.x; i < RB; i += blockDim.x) {
-        const int j = j0 + i;
-        s_len[i] = j < n ? row_ptr[j + 1] - row_ptr[j] : 0;
+    // Cold-start loads that nothing depends on yet: the warp's stream position, the quad-row counts
+    // of every (warp, chunk) of this CTA (one contiguous piece of grp_nq), the row lengths of the
+    // epilogue (kept in a register until then) and L2 prefetches of the C tile updated at the end.
+    const int g = blockIdx.x * nwarps + warp;
+    const bool live = warp < nwarps && g < ngroups;
+    const int64_t s0 = live ? grp_ptr[(int64_t)g * nchunks] : 0;
+    int my_len = 0;
+    if (threadIdx.x < RB && j0 + threadIdx.x < n) my_len = row_ptr[j0 + threadIdx.x + 1] - row_ptr[j0 + threadIdx.x];
+    {
+        const int64_t first = (int64_t)blockIdx.x * nwarps * nchunks, limit = (int64_t)ngroups * nchunks;
+        for (int idx = threadIdx.x; idx < nwarps * nchunks; idx += blockDim.x)
+            s_nq[idx] = first + idx < limit ? grp_nq[first + idx] : 0u;
+        const int lines = (RB + 31) / 32 + 1;                    // 128-byte lines of one C row segment
+        for (int idx = threadIdx.x; idx < MT * lines; idx += blockDim.x) {
+            const int i = idx / lines, l = idx - i * lines;
+            if (m0 + i < m && j0 + l * 32 < n)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(c + (size_t)(m0 + i) * ldc + j0 + l * 32));
+        }
     }
     __syncthreads();
 
-    float4 acc[2][NF4];
+    float4 acc[RS][NF4];
 #pragma unroll
-    for (int rr = 0; rr < 2; ++rr)
+    for (int rr = 0; rr < RS; ++rr)
 #pragma unroll
         for (int f = 0; f < NF4; ++f) acc[rr][f] = make_float4(0.f, 0.f, 0.f, 0.f);
 
@@ -206,185 +226,212 @@ spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__
             for (int ch = 0; ch < nchunks; ++ch) {
                 const int stage = ch % STAGES, round = ch / STAGES;
                 if (round > 0) mbar_wait(&empty[stage], (uint32_t)((round - 1) & 1));
+#ifdef EXP_NOTMA
+                mbar_arrive(&full[stage]);
+#else
                 mbar_expect_tx(&full[stage], CHUNK_BYTES);
                 bulk_g2s(smem_raw + (size_t)stage * STAGE_BYTES, xt_tile + (size_t)ch * kTileK * MT, CHUNK_BYTES,
                          &full[stage]);
+#endif
             }
         }
     } else {
         // ---- consumers ----
-        const int g = blockIdx.x * nwarps + warp;
-        const bool live = g < ngroups;
-        // The warp's quad-row stream -- contiguous over all chunks of its group -- flows through a
-        // private two-half ring.  Each half is filled by one bulk copy; when the warp has read the
-        // last quad row of a half, lane 0 refills that half (ring_turn, off the hot path).
-        const int64_t s0 = live ? grp_ptr[(int64_t)g * nchunks] : 0;
-        const int total = live ? (int)(grp_ptr[(int64_t)(g + 1) * nchunks] - s0) : 0;
         const uint8_t *ring_ptr = ring_base + (size_t)warp * kRingBytes;
         const uint32_t ring = smem_u32(ring_ptr);
-        uint64_t *wbar = wfull + 2 * warp;
-        const uint8_t *stream = blocks + s0 * kBlockBytes;
-        if (lane == 0) {
-            for (int h = 0; h < 2; ++h) {
-                const int cnt = min(kRingHalf, total - h * kRingHalf);
-                if (cnt > 0) {
-                    mbar_expect_tx(&wbar[h], (uint32_t)cnt * kBlockBytes);
-                    bulk_g2s_addr(ring + h * kRingHalf * kBlockBytes, stream + (size_t)h * kRingHalf * kBlockBytes,
-                                  (uint32_t)cnt * kBlockBytes, &wbar[h]);
-                }
-            }
-        }
-        // One quad row is always held in registers ahead of the one being used; `reads` counts the
-        // quad rows taken out of the ring, `left` those still unread in the half `rp` points into.
-        // Reading one quad row past the end of the stream is harmless (stale ring bytes, never used).
-        int reads = 0, left = kRingHalf;
+        const uint8_t *stream = blocks + s0 * kBlockBytes;        // dead warps read (and ignore) the head of the array
+        fetch_segment(ring, stream, 0, lane);
+        fetch_segment(ring, stream, 1, lane);
+        fetch_segment(ring, stream, 2, lane);
+        fetch_segment(ring, stream, 3, lane);
+        // One quad row is always held in registers ahead of the one being used.  `seg` is the segment
+        // the look-ahead read is in, `left` the quad rows not yet read from it.  Reading past the end
+        // of the warp's stream is harmless: the array is padded and the rows are never used.
         const uint8_t *rp = ring_ptr + slot * 16;                // this slot's read pointer into the ring
         const int roff = 64 - slot * 12;                         // from the slot's weights to its offsets
-        if (total > 0) mbar_wait(&wbar[0], 0u);
+        asm volatile("cp.async.wait_group 3;" ::: "memory");
+        __syncwarp();
         float4 cur_w = *reinterpret_cast<const float4 *>(rp);
         uint32_t cur_r = *reinterpret_cast<const uint32_t *>(rp + roff);
         rp += kBlockBytes;
-        reads = 1;
-        left = kRingHalf - 1;
-        uint32_t nq_next = live ? grp_nq[(int64_t)g * nchunks] : 0u;
+        int seg = 0, left = kSegRows - 1;
         const uint32_t xlane = smem_u32(smem_raw) + c8 * 16;
+        const uint32_t *my_nq = s_nq + warp * nchunks;
 
         float4 xr[4][NF4];                                       // X staging registers, one set per step
 #pragma unroll
         for (int t = 0; t < 4; ++t)
 #pragma unroll
             for (int f = 0; f < NF4; ++f) xr[t][f] = make_float4(0.f, 0.f, 0.f, 0.f);
-        // the quad rows of one row pair in the current chunk
-        auto walk_pair = [&](float4 (&a)[NF4], int nq, uint32_t xbase) {
-            while (nq > 0) {                                     // runs that stay inside one ring half
-                const int run = min(nq, left);
-#pragma unroll 1
-                for (int q = 0; q < run; ++q) {
-                    float4 w = cur_w;
-                    const uint32_t r4 = cur_r;
-                    cur_w = *reinterpret_cast<const float4 *>(rp);              // next quad row, ahead of use
-                    cur_r = *reinterpret_cast<const uint32_t *>(rp + roff);
-                    rp += kBlockBytes;
-                    if (SCALE) { w.x *= alpha; w.y *= alpha; w.z *= alpha; w.w *= alpha; }
-                    slot_step<NF4, MT * 4>(a, xr[0], w.x, __byte_perm(r4, 0u, 0x4440u), xbase);
-                    slot_step<NF4, MT * 4>(a, xr[1], w.y, __byte_perm(r4, 0u, 0x4441u), xbase);
-                    slot_step<NF4, MT * 4>(a, xr[2], w.z, __byte_perm(r4, 0u, 0x4442u), xbase);
-                    slot_step<NF4, MT * 4>(a, xr[3], w.w, __byte_perm(r4, 0u, 0x4443u), xbase);
+        // the quad rows of one slot-row set in the current chunk
+        auto walk = [&](float4 (&a)[NF4], int nq, uint32_t xbase) {
+#pragma unroll 2
+            for (int q = 0; q < nq; ++q) {
+                float4 w = cur_w;
+                const uint32_t r4 = cur_r;
+                if (left == 0) {                                 // the look-ahead moves into the next segment
+                    asm volatile("cp.async.wait_group 2;" ::: "memory");
+                    __syncwarp();                                // it has landed for every lane; the one left behind is free
+                    ++seg;
+                    fetch_segment(ring, stream, seg + kRingSegs - 1, lane);
+                    if ((seg & (kRingSegs - 1)) == 0) rp = ring_ptr + slot * 16;
+                    left = kSegRows;
                 }
-                nq -= run;
-                left -= run;
-                reads += run;
-                if (left == 0) {                                 // the look-ahead read was the last of a half
-                    ring_turn(ring, wbar, stream, reads, total, lane);
-                    left = kRingHalf;
-                    if (((reads / kRingHalf) & 1) == 0) rp = ring_ptr + slot * 16;
-                }
+                --left;
+                cur_w = *reinterpret_cast<const float4 *>(rp);   // next quad row, ahead of use
+                cur_r = *reinterpret_cast<const uint32_t *>(rp + roff);
+                rp += kBlockBytes;
+                if (SCALE) { w.x *= alpha; w.y *= alpha; w.z *= alpha; w.w *= alpha; }
+                slot_step<NF4, MT * 4>(a, xr[0], w.x, __byte_perm(r4, 0u, 0x4440u), xbase);
+                slot_step<NF4, MT * 4>(a, xr[1], w.y, __byte_perm(r4, 0u, 0x4441u), xbase);
+                slot_step<NF4, MT * 4>(a, xr[2], w.z, __byte_perm(r4, 0u, 0x4442u), xbase);
+                slot_step<NF4, MT * 4>(a, xr[3], w.w, __byte_perm(r4, 0u, 0x4443u), xbase);
             }
         };
 
         for (int ch = 0; ch < nchunks; ++ch) {
             const int stage = ch % STAGES;
-            const uint32_t nq2 = nq_next;
-            if (live && ch + 1 < nchunks) nq_next = grp_nq[(int64_t)g * nchunks + ch + 1];
+#ifdef EXP_NOCOMPUTE
+            const uint32_t nq2 = 0u;
+#else
+            const uint32_t nq2 = my_nq[ch];
+#endif
             mbar_wait(&full[stage], (uint32_t)((ch / STAGES) & 1));
             const uint32_t xbase = xlane + stage * STAGE_BYTES;
-            walk_pair(acc[0], (int)(nq2 & 0xffffu), xbase);
-            walk_pair(acc[1], (int)(nq2 >> 16), xbase);
+            walk(acc[0], (int)(nq2 & 0xffffu), xbase);
+            if (RS == 2) walk(acc[RS - 1], (int)(nq2 >> 16), xbase);
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[stage]);           // this warp is done with the stage
         }
+        asm volatile("cp.async.wait_group 0;" ::: "memory");     // nothing of the ring is in flight any more
     }
 
     // every warp is past the k loop: the X ring is free, stage the RB x MT result tile in it
+    if (threadIdx.x < RB) s_len[threadIdx.x] = my_len;
     __syncthreads();
     float *tile = reinterpret_cast<float *>(smem_raw);           // [RB][MT + 1]
     if (warp < nwarps) {
 #pragma unroll
-        for (int rr = 0; rr < 2; ++rr)
+        for (int rr = 0; rr < RS; ++rr)
 #pragma unroll
             for (int f = 0; f < NF4; ++f) {
-                float *p = tile + (size_t)(warp * kTileRows + rr * 4 + slot) * (MT + 1) + 32 * f + c8 * 4;
+                float *p = tile + (size_t)(warp * G + rr * 4 + slot) * (MT + 1) + 32 * f + c8 * 4;
                 p[0] = acc[rr][f].x; p[1] = acc[rr][f].y; p[2] = acc[rr][f].z; p[3] = acc[rr][f].w;
             }
     }
     __syncthreads();
-    const int m0 = blockIdx.y * MT;
+    // C[m0+i][j0 .. j0+RB) += tile column i: 128-byte rows along j.  A warp takes kEpi rows of C at
+    // a time and issues all their loads before the first use.
+    constexpr int kEpi = 4, kJ = kMaxRows / 32;
     const int nw_all = blockDim.x >> 5;
-    for (int i = warp; i < MT; i += nw_all) {
-        const int gi = m0 + i;
-        if (gi >= m) break;
-        for (int jl = lane; jl < RB; jl += 32) {
-            const int j = j0 + jl;
-            if (j >= n) break;
-            const int len = s_len[jl];
-            if (len == 0 && beta == 1.0f) continue;              // S column without entries, no scale: untouched
-            float *p = c + (size_t)gi * ldc + j;
-            float c0 = *p;
-            if (beta != 1.0f) c0 *= beta;
-            *p = len ? c0 + tile[(size_t)jl * (MT + 1) + i] : c0;
-        }
+    for (int ib = warp * kEpi; ib < MT && m0 + ib < m; ib += nw_all * kEpi) {
+        float c0[kEpi][kJ];
+#pragma unroll
+        for (int e = 0; e < kEpi; ++e)
+#pragma unroll
+            for (int u = 0; u < kJ; ++u) {
+                const int jl = lane + 32 * u, i = ib + e;
+                c0[e][u] = (i < MT && m0 + i < m && jl < RB && j0 + jl < n) ? c[(size_t)(m0 + i) * ldc + j0 + jl] : 0.0f;
+            }
+#pragma unroll
+        for (int e = 0; e < kEpi; ++e)
+#pragma unroll
+            for (int u = 0; u < kJ; ++u) {
+                const int jl = lane + 32 * u, i = ib + e;
+                if (i >= MT || m0 + i >= m || jl >= RB || j0 + jl >= n) continue;
+                const int len = s_len[jl];
+                if (len == 0 && beta == 1.0f) continue;          // S column without entries, no scale: untouched
+                float v = c0[e][u];
+                if (beta != 1.0f) v *= beta;
+                c[(size_t)(m0 + i) * ldc + j0 + jl] = len ? v + tile[(size_t)jl * (MT + 1) + i] : v;
+            }
     }
 }
 
-template <int NF4, int STAGES>
-static int launch_tile(sblas_b200_matrix *mat, const float *xt, int k_alloc, float *d_c, int ldc, int m, float alpha,
-                       float beta, int nwarps, cudaStream_t stream) {
-    constexpr int MT = 32 * NF4;
-    const size_t smem = (size_t)STAGES * 256 * MT * 4 + (size_t)nwarps * kRingBytes + (2 * STAGES + 2 * nwarps) * 8;
+template <int RS, int NF4, int STAGES>
+static int launch_tile(const sblas_b200_matrix *mat, const TileFormat &tf, const float *xt, int k_alloc, float *d_c,
+                       int ldc, int m, float alpha, float beta, int nwarps, cudaStream_t stream) {
+    constexpr int MT = 32 * NF4, MAXW = kMaxRows / (4 * RS);
+    const int nchunks = tf.nchunks;
+    auto smem_for = [nchunks](int nw) { return (size_t)STAGES * 256 * MT * 4 + (size_t)nw * kRingBytes + 2 * STAGES * 8 + (size_t)nw * nchunks * 4; };
+    if (smem_for(nwarps) > 226 * 1024) return 1;                  // k too long for the per-chunk counts: gather kernel
     static bool configured = false;                              // per template instance
     if (!configured) {
-        const int most = (int)((size_t)STAGES * 256 * MT * 4 + (size_t)kMaxWarps * kRingBytes + (2 * STAGES + 2 * kMaxWarps) * 8);
-        SB_CUDA(cudaFuncSetAttribute(spmm_tile_kernel<NF4, STAGES, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, most));
-        SB_CUDA(cudaFuncSetAttribute(spmm_tile_kernel<NF4, STAGES, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, most));
+        (void)MAXW;
+        SB_CUDA(cudaFuncSetAttribute(spmm_tile_kernel<RS, NF4, STAGES, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+        SB_CUDA(cudaFuncSetAttribute(spmm_tile_kernel<RS, NF4, STAGES, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
         configured = true;
     }
-    const dim3 grid((mat->tile_ngroups + nwarps - 1) / nwarps, (m + MT - 1) / MT);
+    const dim3 grid((tf.ngroups + nwarps - 1) / nwarps, (m + MT - 1) / MT);
     if (alpha == 1.0f)
-        SB_LAUNCH((spmm_tile_kernel<NF4, STAGES, false>), grid, (nwarps + 1) * 32, smem, stream, mat->d_tile_blocks,
-                  mat->d_grp_ptr, mat->d_grp_nq, mat->d_row_ptr, mat->tile_ngroups, mat->tile_nchunks, mat->n, xt,
-                  k_alloc, d_c, ldc, m, alpha, beta, nwarps);
+        SB_LAUNCH((spmm_tile_kernel<RS, NF4, STAGES, false>), grid, (nwarps + 1) * 32, smem_for(nwarps), stream, tf.d_blocks,
+                  tf.d_grp_ptr, tf.d_grp_nq, mat->d_row_ptr, tf.ngroups, tf.nchunks, mat->n, xt, k_alloc, d_c, ldc, m,
+                  alpha, beta, nwarps);
     else
-        SB_LAUNCH((spmm_tile_kernel<NF4, STAGES, true>), grid, (nwarps + 1) * 32, smem, stream, mat->d_tile_blocks,
-                  mat->d_grp_ptr, mat->d_grp_nq, mat->d_row_ptr, mat->tile_ngroups, mat->tile_nchunks, mat->n, xt,
-                  k_alloc, d_c, ldc, m, alpha, beta, nwarps);
+        SB_LAUNCH((spmm_tile_kernel<RS, NF4, STAGES, true>), grid, (nwarps + 1) * 32, smem_for(nwarps), stream, tf.d_blocks,
+                  tf.d_grp_ptr, tf.d_grp_nq, mat->d_row_ptr, tf.ngroups, tf.nchunks, mat->n, xt, k_alloc, d_c, ldc, m,
+                  alpha, beta, nwarps);
     SB_CHECK_LAUNCH();
     return SBLAS_B200_OK;
 }
 
-// Row block height (consumer warps per CTA) that fills the SMs best: one CTA per SM at a time, so
-// the cost of a launch is (waves of CTAs) x (rows per CTA); fewer, taller CTAs re-read X less often.
-static int pick_nwarps(int ngroups, int mtiles, int sms) {
-    int best = kMaxWarps;
-    double best_cost = 1e30;
-    for (int nw = kMaxWarps; nw >= 4; --nw) {
-        const int64_t ctas = (int64_t)((ngroups + nw - 1) / nw) * mtiles;
-        const int64_t waves = (ctas + sms - 1) / sms;
-        const double cost = (double)waves * (nw + 0.75);        // +0.75: per-CTA X fill and prologue/epilogue
-        if (cost < best_cost - 1e-9) { best_cost = cost; best = nw; }
-    }
+namespace {
+struct TilePlan { int rs, nf4, nwarps; };
+
+// Pick rows per slot, float4s per lane and consumer warps per CTA.  One CTA per SM at a time, so a
+// launch costs (waves of CTAs) x (time of one CTA); the time of one CTA is a fixed part (cold start,
+// epilogue) plus quad rows per warp x the time of one quad row, which is bound either by the issue
+// slots its warps share (4 schedulers per SM) or by the dependent latency of one iteration.
+// Constants fitted to B200 measurements (profiles/): cycles.
+TilePlan plan_tile(const sblas_b200_matrix *mat, int m, int sms) {
+    const double fixed = 8000.0, eff = 0.75;
+    const int nchunks = (mat->k + kTileK - 1) / kTileK;
+    const double quads = 1.25 * (double)mat->nnz / std::max(1, mat->n) / 4.0 + 0.5 * nchunks;   // per 4-row set
+    TilePlan best = {2, 1, 16};
+    double best_cost = 1e300;
+    for (int rs = 1; rs <= 2; ++rs)
+        for (int nf4 = 1; nf4 <= 2; ++nf4) {
+            if (nf4 == 2 && m <= 32) continue;
+            const int max_w = (rs == 1 && nf4 == 1) ? 28 : 16;
+            const double instr = nf4 == 1 ? 38.0 : 55.0, lat = nf4 == 1 ? 90.0 : 110.0;
+            const int mtiles = (m + 32 * nf4 - 1) / (32 * nf4);
+            const int ngroups = (mat->n + 4 * rs - 1) / (4 * rs);
+            for (int nw = 4; nw <= max_w; ++nw) {
+                const int64_t ctas = (int64_t)((ngroups + nw - 1) / nw) * mtiles;
+                const int64_t waves = (ctas + sms - 1) / sms;
+                const double per_quad = std::max(instr * ((nw + 3) / 4) / eff, lat);
+                const double cost = (double)waves * (fixed + rs * quads * per_quad);
+                if (cost < best_cost * (1.0 - 1e-9)) { best_cost = cost; best = {rs, nf4, nw}; }
+            }
+        }
     return best;
 }
+}  // namespace
 
-// Variant selection: SBLAS_B200_TILE = "<warps: 4..g(16), hex><float4s per lane: 1|2>" (experiments), else by shape.
+// Variant override for experiments: SBLAS_B200_TILE = "<rows per slot 1|2><float4s per lane 1|2><warps, 2 digits>".
 int run_spmm_tile(sblas_b200_matrix *mat, const float *d_a, int m, int lda, float *d_c, int ldc, float alpha,
                   float beta, cudaStream_t stream) {
     static int sms = 0;
     if (!sms) {
         if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, mat->device) != cudaSuccess || sms <= 0) sms = 148;
     }
-    // two float4 per lane halve the per-entry bookkeeping, but only when that still fills the SMs
-    int nf4 = 1;
-    if (m > 32 && (int64_t)((mat->tile_ngroups + 7) / 8) * ((m + 63) / 64) >= sms) nf4 = 2;
-    int nwarps = 0;
+    TilePlan plan = plan_tile(mat, m, sms);
     if (const char *env = getenv("SBLAS_B200_TILE")) {
-        if (env[0] >= '4' && env[0] <= '9') nwarps = env[0] - '0';
-        else if (env[0] >= 'a' && env[0] <= 'g') nwarps = 10 + (env[0] - 'a');
-        if (env[0] && (env[1] == '1' || env[1] == '2')) nf4 = env[1] - '0';
+        if ((env[0] == '1' || env[0] == '2') && (env[1] == '1' || env[1] == '2') && env[2] && env[3]) {
+            plan.rs = env[0] - '0';
+            plan.nf4 = env[1] - '0';
+            plan.nwarps = std::min((plan.rs == 1 && plan.nf4 == 1) ? 28 : 16, std::max(1, atoi(env + 2)));
+        }
     }
-    const int MT = 32 * nf4;
+    TileFormat &tf = mat->tile[plan.rs == 2];
+    if (tf.state == 0) {
+        const int brc = build_tile_format(mat, 4 * plan.rs, stream);
+        if (brc != SBLAS_B200_OK) return brc;
+    }
+    if (tf.state != 1) return 1;                                  // no tile layout for this matrix: caller falls back to the gather kernel
+    const int MT = 32 * plan.nf4;
     const int ntiles = (m + MT - 1) / MT;
-    if (nwarps == 0) nwarps = pick_nwarps(mat->tile_ngroups, ntiles, sms);
-    const int k_alloc = mat->tile_nchunks * kTileK;
+    const int k_alloc = tf.nchunks * kTileK;
     int rc = ensure_buffer(&mat->d_ws, &mat->ws_bytes, (size_t)ntiles * k_alloc * MT * 4);
     if (rc != SBLAS_B200_OK) return rc;
     const dim3 tgrid((mat->k + 31) / 32, ntiles * MT / 32);
@@ -397,8 +444,11 @@ int run_spmm_tile(sblas_b200_matrix *mat, const float *d_a, int m, int lda, floa
         }
         ~Timer() { if (a) { cudaEventRecord(b, st); mat->prof_events.push_back(std::make_pair(a, b)); } }
     } timer(mat, stream);
-    if (nf4 == 2) return launch_tile<2, 2>(mat, mat->d_ws, k_alloc, d_c, ldc, m, alpha, beta, nwarps, stream);
-    return launch_tile<1, 3>(mat, mat->d_ws, k_alloc, d_c, ldc, m, alpha, beta, nwarps, stream);
+    const float *xt = mat->d_ws;
+    if (plan.rs == 1 && plan.nf4 == 1) return launch_tile<1, 1, 3>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, stream);
+    if (plan.rs == 1) return launch_tile<1, 2, 2>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, stream);
+    if (plan.nf4 == 1) return launch_tile<2, 1, 3>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, stream);
+    return launch_tile<2, 2, 2>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, stream);
 }
 
 }  // namespace sblas_b200

@@ -362,7 +362,7 @@ static void release(sblas_b200_matrix *mat) {
     if (!mat) return;
     cudaFree(mat->d_row_ptr); cudaFree(mat->d_col); cudaFree(mat->d_code); cudaFree(mat->d_table);
     cudaFree(mat->d_long_rows); cudaFree(mat->d_long_seg_ptr); cudaFree(mat->d_seg_begin); cudaFree(mat->d_seg_end);
-    cudaFree(mat->d_tile_blocks); cudaFree(mat->d_grp_ptr); cudaFree(mat->d_grp_nq);
+    for (TileFormat &tf : mat->tile) { cudaFree(tf.d_blocks); cudaFree(tf.d_grp_ptr); cudaFree(tf.d_grp_nq); }
     cudaFree(mat->d_ws); cudaFree(mat->d_partial); cudaFree(mat->d_host_a); cudaFree(mat->d_host_c);
     if (mat->stream) cudaStreamDestroy(mat->stream);
     delete mat;

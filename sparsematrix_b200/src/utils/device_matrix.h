@@ -60,6 +60,18 @@ private:
 
 #define SB_CHECK_LAUNCH() SB_CUDA(cudaGetLastError())
 
+// One SpMM tile layout: row groups of `rows` W rows x chunks of 255 X rows; per (group, chunk) a
+// contiguous run of 80-byte quad rows (per warp slot 4 fp32 weights + 4 one-byte X-row offsets).
+struct TileFormat {
+    int state = 0;                      // 0 = not built yet, 1 = built, -1 = not worthwhile / not possible
+    int rows = 0;                       // W rows per group: 4 or 8
+    uint8_t *d_blocks = nullptr;        // [nblocks + 2][80] quad rows
+    int32_t *d_grp_ptr = nullptr;       // [ngroups * nchunks + 1] first quad row of each (group, chunk)
+    uint32_t *d_grp_nq = nullptr;       // [ngroups * nchunks] quad rows of slot-row 0 | slot-row 1 << 16
+    int32_t ngroups = 0, nchunks = 0;
+    int64_t nblocks = 0;
+};
+
 struct sblas_b200_matrix {
     int device = 0;
     int32_t k = 0;           // rows of S  = length of an X row index space
@@ -95,16 +107,10 @@ struct sblas_b200_matrix {
     cudaStream_t stream = nullptr;                          // host path stream
     int64_t format_bytes = 0;
 
-    // SpMM tile format (src/utils/tile_format.cu), built on the first large-m product.
-    // Row groups of 8 W rows x chunks of 255 X rows; per (group, chunk) a contiguous run of
-    // 80-byte quad rows: per warp slot 4 fp32 weights + 4 one-byte X-row offsets inside the chunk.
-    int tile_state = 0;                 // 0 = not built yet, 1 = built, -1 = not worthwhile / not possible
+    // SpMM tile formats (src/utils/tile_format.cu), built on the first large-m product that wants
+    // them: [0] row groups of 4 W rows (one per warp slot), [1] groups of 8 (two per slot).
     bool csr_sorted = true;             // columns ascending inside every row (required by the tile build)
-    uint8_t *d_tile_blocks = nullptr;   // [tile_nblocks + 2][80] quad rows
-    int32_t *d_grp_ptr = nullptr;       // [tile_ngroups * tile_nchunks + 1] first block of each (group, chunk)
-    uint32_t *d_grp_nq = nullptr;       // [tile_ngroups * tile_nchunks] quad rows of row pair 0 | pair 1 << 16
-    int32_t tile_ngroups = 0, tile_nchunks = 0;
-    int64_t tile_nblocks = 0;
+    TileFormat tile[2];
 
     // sblas_b200_profile_begin/_end: event pairs around the dominant kernel
     bool profiling = false;
@@ -117,10 +123,10 @@ int plan_spmv(sblas_b200_matrix *mat, const int32_t *h_row_ptr);
 int ensure_buffer(float **buf, size_t *have, size_t need);
 int exclusive_scan_i32(const int32_t *d_in, int n, int32_t *d_out, cudaStream_t stream);   // d_out[n] = total
 // src/utils/tile_format.cu
-constexpr int kTileRows = 8;         // W rows per group = one warp's share of a CTA's row block
 constexpr int kTileK = 255;          // X rows per chunk; offset 255 addresses an all-zero row (padding entries)
 constexpr int kBlockBytes = 80;
-int build_tile_format(sblas_b200_matrix *mat, cudaStream_t stream);
+constexpr int kTilePad = 48;         // quad rows of slack after the last one (ring segments fetched ahead)
+int build_tile_format(sblas_b200_matrix *mat, int rows_per_group, cudaStream_t stream);
 // src/sparse/spmm_tile.cu
 int run_spmm_tile(sblas_b200_matrix *mat, const float *d_a, int m, int lda, float *d_c, int ldc, float alpha,
                   float beta, cudaStream_t stream);

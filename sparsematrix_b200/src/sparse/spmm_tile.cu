@@ -27,6 +27,7 @@
 // the function of the reference's per-panel C transposes (sparse-matrix.cc:184,189).  beta is
 // applied there (only when != 1, sparse-matrix.cc:149), alpha is folded into the weights first
 // (kernel.cc:791).
+#include <stdio.h>
 #include <stdlib.h>
 
 #include <algorithm>
@@ -70,6 +71,18 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
 }
 
 constexpr int kMaxRows = 128;                                   // W rows per CTA at most
+
+#ifdef EXP_TIMELINE
+__device__ unsigned long long g_timeline[2048 * 8];
+__device__ __forceinline__ unsigned long long gtime() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define TL(p) do { if (threadIdx.x == 0) g_timeline[(blockIdx.y * gridDim.x + blockIdx.x) * 8 + (p)] = gtime(); } while (0)
+#else
+#define TL(p) do { } while (0)
+#endif
 
 // The warp's quad-row stream goes through a private ring of kRingSegs segments of kSegRows quad rows;
 // a segment is fetched by the warp itself with 16-byte cp.async (LDGSTS) three segments ahead.
@@ -189,6 +202,7 @@ spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__
     const int m0 = blockIdx.y * MT;
     const float *xt_tile = xt + (size_t)blockIdx.y * k_alloc * MT;
 
+    TL(0);
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], nwarps); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -213,6 +227,7 @@ spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__
         }
     }
     __syncthreads();
+    TL(1);
 
     float4 acc[RS][NF4];
 #pragma unroll
@@ -251,6 +266,7 @@ spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__
         const int roff = 64 - slot * 12;                         // from the slot's weights to its offsets
         asm volatile("cp.async.wait_group 3;" ::: "memory");
         __syncwarp();
+        TL(2);
         float4 cur_w = *reinterpret_cast<const float4 *>(rp);
         uint32_t cur_r = *reinterpret_cast<const uint32_t *>(rp + roff);
         rp += kBlockBytes;
@@ -289,6 +305,7 @@ spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__
             }
         };
 
+
         for (int ch = 0; ch < nchunks; ++ch) {
             const int stage = ch % STAGES;
 #ifdef EXP_NOCOMPUTE
@@ -297,6 +314,7 @@ spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__
             const uint32_t nq2 = my_nq[ch];
 #endif
             mbar_wait(&full[stage], (uint32_t)((ch / STAGES) & 1));
+            if (ch == 0) TL(3);
             const uint32_t xbase = xlane + stage * STAGE_BYTES;
             walk(acc[0], (int)(nq2 & 0xffffu), xbase);
             if (RS == 2) walk(acc[RS - 1], (int)(nq2 >> 16), xbase);
@@ -304,11 +322,13 @@ spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__
             if (lane == 0) mbar_arrive(&empty[stage]);           // this warp is done with the stage
         }
         asm volatile("cp.async.wait_group 0;" ::: "memory");     // nothing of the ring is in flight any more
+        TL(4);
     }
 
     // every warp is past the k loop: the X ring is free, stage the RB x MT result tile in it
     if (threadIdx.x < RB) s_len[threadIdx.x] = my_len;
     __syncthreads();
+    TL(5);
     float *tile = reinterpret_cast<float *>(smem_raw);           // [RB][MT + 1]
     if (warp < nwarps) {
 #pragma unroll
@@ -346,7 +366,26 @@ spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__
                 c[(size_t)(m0 + i) * ldc + j0 + jl] = len ? v + tile[(size_t)jl * (MT + 1) + i] : v;
             }
     }
+    TL(6);
 }
+
+#ifdef EXP_TIMELINE
+static int g_tl_ctas = 0;
+static void dump_timeline() {
+    static unsigned long long h[2048 * 8];
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(h, g_timeline, sizeof(h));
+    const int n = std::min(g_tl_ctas, 2048);
+    unsigned long long t0 = ~0ull;
+    for (int i = 0; i < n; ++i) t0 = std::min(t0, h[i * 8]);
+    double avg[7] = {0}, mx[7] = {0};
+    for (int i = 0; i < n; ++i)
+        for (int p = 0; p < 7; ++p) { const double d = (double)(h[i * 8 + p] - t0) * 1e-3; avg[p] += d / n; mx[p] = std::max(mx[p], d); }
+    fprintf(stderr, "timeline (us since first CTA start; avg / max over %d CTAs of the last launch):\n", n);
+    const char *names[7] = {"start", "prologue done", "stream ring ready", "first X chunk landed", "k loop done (warp 0)", "all warps done", "end"};
+    for (int p = 0; p < 7; ++p) fprintf(stderr, "  %-22s %8.2f %8.2f\n", names[p], avg[p], mx[p]);
+}
+#endif
 
 template <int RS, int NF4, int STAGES>
 static int launch_tile(const sblas_b200_matrix *mat, const TileFormat &tf, const float *xt, int k_alloc, float *d_c,
@@ -363,6 +402,9 @@ static int launch_tile(const sblas_b200_matrix *mat, const TileFormat &tf, const
         configured = true;
     }
     const dim3 grid((tf.ngroups + nwarps - 1) / nwarps, (m + MT - 1) / MT);
+#ifdef EXP_TIMELINE
+    { static bool reg = false; if (!reg) { atexit(dump_timeline); reg = true; } g_tl_ctas = grid.x * grid.y; }
+#endif
     if (alpha == 1.0f)
         SB_LAUNCH((spmm_tile_kernel<RS, NF4, STAGES, false>), grid, (nwarps + 1) * 32, smem_for(nwarps), stream, tf.d_blocks,
                   tf.d_grp_ptr, tf.d_grp_nq, mat->d_row_ptr, tf.ngroups, tf.nchunks, mat->n, xt, k_alloc, d_c, ldc, m,

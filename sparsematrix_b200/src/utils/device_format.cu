@@ -262,6 +262,23 @@ __global__ void csr_sorted_kernel(const int32_t *__restrict__ row_ptr, const int
         if (col[e] <= col[e - 1]) atomicOr(bad, 2);
 }
 
+// Sorted SpMV layout: warp per sorted position copies its row, padding the last block (col 0, code 255).
+__global__ void __launch_bounds__(256)
+sorted_copy_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col, const uint8_t *__restrict__ code,
+                   const int32_t *__restrict__ order, const int32_t *__restrict__ blk_ptr, int n_ordered,
+                   int32_t *__restrict__ scol, uint8_t *__restrict__ scode) {
+    const int i = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (i >= n_ordered) return;
+    const int row = order[i];
+    const int s = row_ptr[row], len = row_ptr[row + 1] - s;
+    const int64_t d = (int64_t)blk_ptr[i] * 4;
+    const int padded = (len + 3) & ~3;
+    for (int e = lane; e < padded; e += 32) {
+        scol[d + e] = e < len ? col[s + e] : 0;
+        scode[d + e] = e < len ? code[s + e] : (uint8_t)255;
+    }
+}
+
 // K-decode: CSR(W) -> dense, the function of CopyTo (sparse-matrix.cc:101-137).  Warp per W row.
 __global__ void __launch_bounds__(256)
 decode_dense_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
@@ -329,6 +346,51 @@ int plan_spmv(sblas_b200_matrix *mat, const int32_t *h_row_ptr) {
     }
     mat->n_long = (int32_t)long_rows.size();
     mat->n_long_seg = (int32_t)seg_b.size();
+    // Skewed row lengths: a warp is as slow as its longest row, so rows are visited in order of
+    // decreasing length (counting sort) and a warp's rows are about equally long.
+    bool sort_rows = n >= 65536 && (double)max_len >= 4.0 * std::max(1.0, mean);
+    if (const char *env = getenv("SBLAS_B200_SORT_ROWS")) sort_rows = env[0] == '1';
+    if (sort_rows) {
+        const int32_t cap = mat->long_threshold;
+        std::vector<int32_t> count((size_t)cap + 2, 0), order;
+        for (int j = 0; j < n; ++j) {
+            const int32_t len = h_row_ptr[j + 1] - h_row_ptr[j];
+            if (len <= cap) ++count[cap - len + 1];              // bucket 0 = longest
+        }
+        for (int32_t b = 0; b <= cap; ++b) count[b + 1] += count[b];
+        order.resize((size_t)count[cap + 1]);
+        for (int j = 0; j < n; ++j) {
+            const int32_t len = h_row_ptr[j + 1] - h_row_ptr[j];
+            if (len <= cap) order[(size_t)count[cap - len]++] = j;
+        }
+        mat->n_ordered = (int32_t)order.size();
+        if (mat->n_ordered) {
+            std::vector<int32_t> blk_ptr(order.size() + 1, 0), slen(order.size());
+            int64_t blocks = 0;
+            for (size_t i = 0; i < order.size(); ++i) {
+                blk_ptr[i] = (int32_t)blocks;
+                slen[i] = h_row_ptr[order[i] + 1] - h_row_ptr[order[i]];
+                blocks += (slen[i] + 3) >> 2;
+            }
+            blk_ptr[order.size()] = (int32_t)blocks;
+            if (blocks >= ((int64_t)1 << 31)) return fail(SBLAS_B200_EINVAL, "sorted SpMV layout does not fit int32 blocks");
+            mat->sorted_blocks = blocks;
+            SB_CUDA(cudaMalloc((void **)&mat->d_row_order, order.size() * 4));
+            SB_CUDA(cudaMalloc((void **)&mat->d_sblk_ptr, blk_ptr.size() * 4));
+            SB_CUDA(cudaMalloc((void **)&mat->d_slen, slen.size() * 4));
+            SB_CUDA(cudaMalloc((void **)&mat->d_scol, (size_t)(blocks + 1) * 16));
+            SB_CUDA(cudaMalloc((void **)&mat->d_scode, (size_t)(blocks + 1) * 4));
+            SB_CUDA(cudaMemcpy(mat->d_row_order, order.data(), order.size() * 4, cudaMemcpyHostToDevice));
+            SB_CUDA(cudaMemcpy(mat->d_sblk_ptr, blk_ptr.data(), blk_ptr.size() * 4, cudaMemcpyHostToDevice));
+            SB_CUDA(cudaMemcpy(mat->d_slen, slen.data(), slen.size() * 4, cudaMemcpyHostToDevice));
+            SB_LAUNCH(sorted_copy_kernel, (mat->n_ordered + 7) / 8, 256, 0, 0, mat->d_row_ptr, mat->d_col, mat->d_code,
+                      mat->d_row_order, mat->d_sblk_ptr, mat->n_ordered, reinterpret_cast<int32_t *>(mat->d_scol),
+                      reinterpret_cast<uint8_t *>(mat->d_scode));
+            SB_CHECK_LAUNCH();
+            SB_CUDA(cudaDeviceSynchronize());
+            mat->format_bytes += (int64_t)order.size() * 12 + 4 + (blocks + 1) * 20;
+        }
+    }
     if (mat->n_long) {
         SB_CUDA(cudaMalloc((void **)&mat->d_long_rows, long_rows.size() * 4));
         SB_CUDA(cudaMalloc((void **)&mat->d_long_seg_ptr, seg_ptr.size() * 4));
@@ -361,6 +423,7 @@ static int alloc_csr(sblas_b200_matrix *mat, const float *table) {
 static void release(sblas_b200_matrix *mat) {
     if (!mat) return;
     cudaFree(mat->d_row_ptr); cudaFree(mat->d_col); cudaFree(mat->d_code); cudaFree(mat->d_table);
+    cudaFree(mat->d_row_order); cudaFree(mat->d_sblk_ptr); cudaFree(mat->d_slen); cudaFree(mat->d_scol); cudaFree(mat->d_scode);
     cudaFree(mat->d_long_rows); cudaFree(mat->d_long_seg_ptr); cudaFree(mat->d_seg_begin); cudaFree(mat->d_seg_end);
     for (TileFormat &tf : mat->tile) { cudaFree(tf.d_blocks); cudaFree(tf.d_grp_ptr); cudaFree(tf.d_grp_nq); }
     cudaFree(mat->d_ws); cudaFree(mat->d_partial); cudaFree(mat->d_host_a); cudaFree(mat->d_host_c);

@@ -92,6 +92,15 @@ struct sblas_b200_matrix {
     int spmv_lanes = 8;             // sub-warp width for the row-split kernel
     int32_t long_threshold = INT32_MAX;  // rows longer than this take the split-row path
     int32_t n_long = 0, n_long_seg = 0, max_row_nnz = 0;
+    // Skewed row lengths only: a second copy of the short rows, sorted by decreasing length, every
+    // row starting on a block of 4 entries (tail padded with col 0 / code 255 = weight 0, never used).
+    int32_t *d_row_order = nullptr;     // [n_ordered]     original row of sorted position i
+    int32_t *d_sblk_ptr = nullptr;      // [n_ordered + 1] first block (4 entries) of sorted position i
+    int32_t *d_slen = nullptr;          // [n_ordered]     entries of that row
+    int4 *d_scol = nullptr;             // [sorted_blocks] column indices
+    uint32_t *d_scode = nullptr;        // [sorted_blocks] four codes
+    int32_t n_ordered = 0;
+    int64_t sorted_blocks = 0;
     int32_t *d_long_rows = nullptr;     // [n_long]      row index
     int32_t *d_long_seg_ptr = nullptr;  // [n_long+1]    first segment of each long row
     int32_t *d_seg_begin = nullptr;     // [n_long_seg]  element range of a segment

@@ -161,6 +161,7 @@ __global__ void __launch_bounds__(256)
 transpose_in_tiled_kernel(const float *__restrict__ a, int m, int k, int lda, float *__restrict__ xt, int k_alloc,
                           int MT) {
     __shared__ float tile[32][33];
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // the SpMM kernel may start its prologue
     const int r0 = blockIdx.x * 32, i0 = blockIdx.y * 32;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     for (int ii = ty; ii < 32; ii += 8) {
@@ -238,6 +239,7 @@ spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__
     if (warp == nwarps) {
         // ---- producer: keep the X ring full ----
         if (lane == 0) {
+            asm volatile("griddepcontrol.wait;" ::: "memory");   // X^T is written by the kernel before this one
             for (int ch = 0; ch < nchunks; ++ch) {
                 const int stage = ch % STAGES, round = ch / STAGES;
                 if (round > 0) mbar_wait(&empty[stage], (uint32_t)((round - 1) & 1));
@@ -405,14 +407,24 @@ static int launch_tile(const sblas_b200_matrix *mat, const TileFormat &tf, const
 #ifdef EXP_TIMELINE
     { static bool reg = false; if (!reg) { atexit(dump_timeline); reg = true; } g_tl_ctas = grid.x * grid.y; }
 #endif
-    if (alpha == 1.0f)
-        SB_LAUNCH((spmm_tile_kernel<RS, NF4, STAGES, false>), grid, (nwarps + 1) * 32, smem_for(nwarps), stream, tf.d_blocks,
-                  tf.d_grp_ptr, tf.d_grp_nq, mat->d_row_ptr, tf.ngroups, tf.nchunks, mat->n, xt, k_alloc, d_c, ldc, m,
-                  alpha, beta, nwarps);
-    else
-        SB_LAUNCH((spmm_tile_kernel<RS, NF4, STAGES, true>), grid, (nwarps + 1) * 32, smem_for(nwarps), stream, tf.d_blocks,
-                  tf.d_grp_ptr, tf.d_grp_nq, mat->d_row_ptr, tf.ngroups, tf.nchunks, mat->n, xt, k_alloc, d_c, ldc, m,
-                  alpha, beta, nwarps);
+    // Programmatic dependent launch: this kernel may start while the transpose before it in the stream
+    // is still draining; only the producer warp's X copies wait for it (griddepcontrol.wait).
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3((nwarps + 1) * 32);
+    cfg.dynamicSmemBytes = smem_for(nwarps);
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    const int ngroups = tf.ngroups, n = mat->n;
+    auto kernel = alpha == 1.0f ? spmm_tile_kernel<RS, NF4, STAGES, false> : spmm_tile_kernel<RS, NF4, STAGES, true>;
+    SB_CUDA(cudaLaunchKernelEx(&cfg, kernel, (const uint8_t *)tf.d_blocks, (const int32_t *)tf.d_grp_ptr,
+                               (const uint32_t *)tf.d_grp_nq, (const int32_t *)mat->d_row_ptr, ngroups, nchunks, n, xt,
+                               k_alloc, d_c, ldc, m, alpha, beta, nwarps));
+    g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
     SB_CHECK_LAUNCH();
     return SBLAS_B200_OK;
 }

@@ -426,6 +426,161 @@ static int check_product_args(const sblas_b200_matrix *mat, const float *a, int3
     return SBLAS_B200_OK;
 }
 
+// ---- host entry point with pinned caller buffers: copies overlapped with the product --------
+// The product needs A at its start but C only in its last step (out = scale(c) + sum, every
+// kernel above).  So the sum is formed in a device buffer P while C is still travelling in on a
+// second stream, and one kernel then applies  out = len ? scale(c) + p : scale(c)  -- the same
+// two roundings as the fused epilogues -- writing straight into the caller's (mapped) C.
+// P is kept at -0.0f between calls: with beta = 1 the product kernels leave (-0) + sum = sum in it,
+// bit for bit (also when the sum is -0), and the combine kernel puts -0 back as it reads.
+__global__ void __launch_bounds__(256)
+fill_negzero_kernel(float4 *__restrict__ p, size_t n4) {
+    const float z = __int_as_float(0x80000000);
+    for (size_t i = blockIdx.x * (size_t)256 + threadIdx.x; i < n4; i += (size_t)gridDim.x * 256)
+        p[i] = make_float4(z, z, z, z);
+}
+
+template <bool VEC>
+__global__ void __launch_bounds__(256)
+combine_out_kernel(const float *__restrict__ c_in, float *__restrict__ p, const int32_t *__restrict__ row_ptr,
+                   float *__restrict__ out, int ldo, int m, int n, float beta) {
+    const float z = __int_as_float(0x80000000);
+    if (VEC) {
+        const int n4 = n >> 2;
+        const size_t total = (size_t)m * n4;
+        for (size_t idx = blockIdx.x * (size_t)256 + threadIdx.x; idx < total; idx += (size_t)gridDim.x * 256) {
+            const int i = (int)(idx / n4), j = (int)(idx % n4) << 2;
+            float4 cv = *reinterpret_cast<const float4 *>(c_in + (size_t)i * n + j);
+            const float4 pv = *reinterpret_cast<const float4 *>(p + (size_t)i * n + j);
+            *reinterpret_cast<float4 *>(p + (size_t)i * n + j) = make_float4(z, z, z, z);
+            const int r0 = row_ptr[j], r1 = row_ptr[j + 1], r2 = row_ptr[j + 2], r3 = row_ptr[j + 3], r4 = row_ptr[j + 4];
+            if (beta != 1.0f) { cv.x *= beta; cv.y *= beta; cv.z *= beta; cv.w *= beta; }
+            if (r1 != r0) cv.x += pv.x;
+            if (r2 != r1) cv.y += pv.y;
+            if (r3 != r2) cv.z += pv.z;
+            if (r4 != r3) cv.w += pv.w;
+            *reinterpret_cast<float4 *>(out + (size_t)i * ldo + j) = cv;
+        }
+    } else {
+        const size_t total = (size_t)m * n;
+        for (size_t idx = blockIdx.x * (size_t)256 + threadIdx.x; idx < total; idx += (size_t)gridDim.x * 256) {
+            const int i = (int)(idx / n), j = (int)(idx % n);
+            float cv = c_in[idx];
+            const float pv = p[idx];
+            p[idx] = z;
+            if (beta != 1.0f) cv *= beta;
+            if (row_ptr[j + 1] != row_ptr[j]) cv += pv;
+            out[(size_t)i * ldo + j] = cv;
+        }
+    }
+}
+
+// device alias of a pinned + mapped host pointer, or null (pageable memory, or SBLAS_B200_HOST_OVERLAP=0)
+static float *mapped_pointer(const void *host) {
+    static const int enabled = [] { const char *e = getenv("SBLAS_B200_HOST_OVERLAP"); return e ? atoi(e) : 1; }();
+    if (!enabled) return nullptr;
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, host) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    if (attr.type != cudaMemoryTypeHost || !attr.devicePointer) return nullptr;
+    return static_cast<float *>(attr.devicePointer);
+}
+
+// Rows of A / C per slice of the host path: large m is cut so that slice i+1 travels in and slice
+// i-1 travels out while slice i is multiplied.  Slices are multiples of 64 rows (whole m-tiles of
+// the SpMM kernel); SBLAS_B200_HOST_SLICE_ROWS overrides (0 = never slice).
+static int host_slice_rows(const sblas_b200_matrix *mat, int m) {
+    static const int env_rows = [] { const char *e = getenv("SBLAS_B200_HOST_SLICE_ROWS"); return e ? atoi(e) : -1; }();
+    int rows = env_rows;
+    if (rows < 0) {
+        // a slice is at least one m-tile of the SpMM kernel (64 rows) and carries enough bytes to be
+        // worth an extra round of launches (>= 4 MB of A); measured on config 3 (profiles/r01_e2e.md)
+        rows = 64;
+        while ((size_t)rows * mat->k * 4 < ((size_t)4 << 20) && rows < m) rows *= 2;
+        if (m < 2 * rows) rows = 0;
+    }
+    if (rows <= 0 || rows >= m) return m;
+    rows = (rows + 63) & ~63;
+    if ((m + rows - 1) / rows > 16) rows = (((m + 15) / 16) + 63) & ~63;
+    return rows;
+}
+
+static int host_product_overlapped(sblas_b200_matrix *mat, const float *a, int m, int lda, float *c, float *c_mapped,
+                                   int ldc, float alpha, float beta) {
+    const int n = mat->n, k = mat->k;
+    const size_t elems = (size_t)m * n, padded = (elems + 3) & ~(size_t)3;
+    const int rows = host_slice_rows(mat, m);
+    const int slices = (m + rows - 1) / rows;
+    if (!mat->stream2) SB_CUDA(cudaStreamCreateWithFlags(&mat->stream2, cudaStreamNonBlocking));
+    if (!mat->stream3) SB_CUDA(cudaStreamCreateWithFlags(&mat->stream3, cudaStreamNonBlocking));
+    while ((int)mat->host_events.size() < 3 * slices) {
+        cudaEvent_t ev;
+        SB_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        mat->host_events.push_back(ev);
+    }
+    const size_t had = mat->host_p_bytes;
+    int rc = ensure_buffer(&mat->d_host_p, &mat->host_p_bytes, padded * 4);
+    if (rc != SBLAS_B200_OK) return rc;
+    if (mat->host_p_bytes != had) mat->host_p_clean = false;
+    if (!mat->host_p_clean) {
+        const size_t n4 = mat->host_p_bytes / 16;
+        SB_LAUNCH(fill_negzero_kernel, (unsigned)std::min<size_t>((n4 + 255) / 256, 148 * 8), 256, 0, mat->stream,
+                  reinterpret_cast<float4 *>(mat->d_host_p), n4);
+        SB_CHECK_LAUNCH();
+    }
+    mat->host_p_clean = false;                          // until every combine kernel of this call has run
+    auto fail_sync = [&](int code) { cudaStreamSynchronize(mat->stream2); cudaStreamSynchronize(mat->stream3);
+                                     cudaStreamSynchronize(mat->stream); return code; };
+    auto copy_in = [&](bool is_a, int s) -> cudaError_t {
+        const int i0 = s * rows, mi = std::min(rows, m - i0);
+        cudaError_t e = is_a
+            ? cudaMemcpy2DAsync(mat->d_host_a + (size_t)i0 * k, (size_t)k * 4, a + (size_t)i0 * lda, (size_t)lda * 4,
+                                (size_t)k * 4, mi, cudaMemcpyHostToDevice, mat->stream2)
+            : cudaMemcpy2DAsync(mat->d_host_c + (size_t)i0 * n, (size_t)n * 4, c + (size_t)i0 * ldc, (size_t)ldc * 4,
+                                (size_t)n * 4, mi, cudaMemcpyHostToDevice, mat->stream2);
+        if (e == cudaSuccess) e = cudaEventRecord(mat->host_events[3 * s + (is_a ? 0 : 1)], mat->stream2);
+        return e;
+    };
+    // copy engine order: A0, A1, C0, A2, C1, ... -- the next product's input before this one's C
+    cudaError_t e = copy_in(true, 0);
+    for (int s = 0; s < slices && e == cudaSuccess; ++s) {
+        if (s + 1 < slices) e = copy_in(true, s + 1);
+        if (e == cudaSuccess) e = copy_in(false, s);
+    }
+    if (e != cudaSuccess) return fail_sync(cuda_fail(e, "host path copies in", __FILE__, __LINE__));
+    const bool direct = slices == 1;                    // one slice: the combine kernel writes the caller's C itself
+    for (int s = 0; s < slices; ++s) {
+        const int i0 = s * rows, mi = std::min(rows, m - i0);
+        float *p = mat->d_host_p + (size_t)i0 * n, *cs = mat->d_host_c + (size_t)i0 * n;
+        e = cudaStreamWaitEvent(mat->stream, mat->host_events[3 * s], 0);
+        if (e != cudaSuccess) return fail_sync(cuda_fail(e, "host path wait A", __FILE__, __LINE__));
+        rc = product_on_stream(mat, mat->d_host_a + (size_t)i0 * k, mi, k, p, n, alpha, 1.0f, mat->stream);
+        if (rc != SBLAS_B200_OK) return fail_sync(rc);
+        e = cudaStreamWaitEvent(mat->stream, mat->host_events[3 * s + 1], 0);
+        if (e != cudaSuccess) return fail_sync(cuda_fail(e, "host path wait C", __FILE__, __LINE__));
+        float *out = direct ? c_mapped : cs;
+        const int ldo = direct ? ldc : n;
+        const size_t se = (size_t)mi * n;
+        const bool vec = (n & 3) == 0 && (ldo & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+        const size_t work = vec ? se / 4 : se;
+        const unsigned grid = (unsigned)std::min<size_t>((work + 255) / 256, 148 * 16);
+        if (vec) SB_LAUNCH(combine_out_kernel<true>, grid, 256, 0, mat->stream, cs, p, mat->d_row_ptr, out, ldo, mi, n, beta);
+        else SB_LAUNCH(combine_out_kernel<false>, grid, 256, 0, mat->stream, cs, p, mat->d_row_ptr, out, ldo, mi, n, beta);
+        e = cudaGetLastError();
+        if (e == cudaSuccess && !direct) {
+            e = cudaEventRecord(mat->host_events[3 * s + 2], mat->stream);
+            if (e == cudaSuccess) e = cudaStreamWaitEvent(mat->stream3, mat->host_events[3 * s + 2], 0);
+            if (e == cudaSuccess)
+                e = cudaMemcpy2DAsync(c + (size_t)i0 * ldc, (size_t)ldc * 4, cs, (size_t)n * 4, (size_t)n * 4, mi,
+                                      cudaMemcpyDeviceToHost, mat->stream3);
+        }
+        if (e != cudaSuccess) return fail_sync(cuda_fail(e, "host path combine / copy out", __FILE__, __LINE__));
+    }
+    SB_CUDA(cudaStreamSynchronize(mat->stream));
+    if (!direct) SB_CUDA(cudaStreamSynchronize(mat->stream3));
+    mat->host_p_clean = true;
+    return SBLAS_B200_OK;
+}
+
 }  // namespace sblas_b200
 
 using namespace sblas_b200;
@@ -483,13 +638,16 @@ int sblas_b200_addmatmat_host(sblas_b200_matrix *mat, const float *a, int32_t m,
     const int n = mat->n, k = mat->k;
     if (!mat->stream) SB_CUDA(cudaStreamCreateWithFlags(&mat->stream, cudaStreamNonBlocking));
     const bool need_a = alpha != 0.0f && mat->nnz != 0;
+    if (beta == 1.0f && !need_a) return SBLAS_B200_OK;  // nothing changes C
     if (need_a) {
         rc = ensure_buffer(&mat->d_host_a, &mat->host_a_bytes, (size_t)m * k * 4);
         if (rc != SBLAS_B200_OK) return rc;
     }
     rc = ensure_buffer(&mat->d_host_c, &mat->host_c_bytes, (size_t)m * n * 4);
     if (rc != SBLAS_B200_OK) return rc;
-    if (beta == 1.0f && !need_a) return SBLAS_B200_OK;  // nothing changes C
+    float *c_mapped = need_a ? mapped_pointer(c) : nullptr;
+    if (c_mapped) return host_product_overlapped(mat, a, m, lda, c, c_mapped, ldc, alpha, beta);
+    // pageable caller memory (or scale only): copies and kernels back to back on one stream
     if (need_a)
         SB_CUDA(cudaMemcpy2DAsync(mat->d_host_a, (size_t)k * 4, a, (size_t)lda * 4, (size_t)k * 4, m,
                                   cudaMemcpyHostToDevice, mat->stream));

@@ -427,7 +427,11 @@ static void release(sblas_b200_matrix *mat) {
     cudaFree(mat->d_long_rows); cudaFree(mat->d_long_seg_ptr); cudaFree(mat->d_seg_begin); cudaFree(mat->d_seg_end);
     for (TileFormat &tf : mat->tile) { cudaFree(tf.d_blocks); cudaFree(tf.d_grp_ptr); cudaFree(tf.d_grp_nq); }
     cudaFree(mat->d_ws); cudaFree(mat->d_partial); cudaFree(mat->d_host_a); cudaFree(mat->d_host_c);
+    cudaFree(mat->d_host_p);
     if (mat->stream) cudaStreamDestroy(mat->stream);
+    if (mat->stream2) cudaStreamDestroy(mat->stream2);
+    if (mat->stream3) cudaStreamDestroy(mat->stream3);
+    for (cudaEvent_t ev : mat->host_events) cudaEventDestroy(ev);
     delete mat;
 }
 

@@ -114,6 +114,12 @@ struct sblas_b200_matrix {
     float *d_host_a = nullptr;  size_t host_a_bytes = 0;   // host path: A on device
     float *d_host_c = nullptr;  size_t host_c_bytes = 0;   // host path: C on device
     cudaStream_t stream = nullptr;                          // host path stream
+    // host path, pinned caller buffers: the product runs into d_host_p (kept at -0.0f between calls)
+    // while C travels in on stream2; one kernel then combines both straight into the caller's C
+    float *d_host_p = nullptr;  size_t host_p_bytes = 0;   bool host_p_clean = false;
+    // and, for large m, in slices of A/C rows so that copies in, products and copies out overlap
+    cudaStream_t stream2 = nullptr, stream3 = nullptr;  // copies in / copies out
+    std::vector<cudaEvent_t> host_events;                // per slice: A arrived, C arrived, result ready
     int64_t format_bytes = 0;
 
     // SpMM tile formats (src/utils/tile_format.cu), built on the first large-m product that wants

@@ -19,7 +19,7 @@
 // pieces are filled with "no entry" -- those lanes are predicated off in the kernel and cost
 // no shared-memory bandwidth.
 // grp_ptr[group*nchunks + chunk] = first quad row of the run;
-// grp_nq[group*nchunks + chunk]  = quad rows of pair 0 | quad rows of pair 1 << 16.
+// grp_nq[group*nchunks + chunk]  = quad rows of rows 0..3 | quad rows of rows 4..7 << 16 (0 when G = 4).
 #include <stdlib.h>
 
 #include <algorithm>
@@ -78,8 +78,8 @@ tile_fill_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restrict_
     const int jj = (int)(idx % G);
     const int64_t gc = idx / G;
     const uint32_t nq2 = grp_nq[gc];
-    const int pair = jj >> 2, slot = jj & 3;
-    const int nq = pair ? (int)(nq2 >> 16) : (int)(nq2 & 0xffffu);
+    const int set = jj >> 2, slot = jj & 3;
+    const int nq = set ? (int)(nq2 >> 16) : (int)(nq2 & 0xffffu);
     if (nq == 0) return;
     const int c = (int)(gc % nchunks), g = (int)(gc / nchunks);
     const int j = g * G + jj;
@@ -89,7 +89,7 @@ tile_fill_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restrict_
         lo = lower_bound_col(col, s, e, c * kTileK);
         len = lower_bound_col(col, lo, e, (c + 1) * kTileK) - lo;
     }
-    const int64_t first = (int64_t)grp_ptr[gc] + (pair ? (int)(nq2 & 0xffffu) : 0);
+    const int64_t first = (int64_t)grp_ptr[gc] + (set ? (int)(nq2 & 0xffffu) : 0);
     for (int q = 0; q < nq; ++q) {
         uint8_t *blk = blocks + (first + q) * kBlockBytes;
         float4 w = make_float4(0.f, 0.f, 0.f, 0.f);

@@ -297,3 +297,43 @@ def test_cpp_harness_binaries(binary, expect):
         pytest.skip(f"{binary} not built")
     out = subprocess.run([path], capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and expect in out.stdout, out.stdout[-2000:] + out.stderr[-500:]
+
+
+# ------------------------------------------------------------------ host entry point, pinned caller buffers
+def test_pinned_host_buffers_give_the_same_bits_as_pageable_ones():
+    """Pinned A/C take the overlapped route (product into a side buffer while C travels in, one
+    combine kernel writing into the caller's C); pageable buffers take copy-product-copy.  Both
+    must produce identical bits, incl. columns without entries, -0, ragged ldc and repeated calls."""
+    import torch
+    n, k = 777, 1000
+    codes = gen.codes_bernoulli(n, k, 0.04, seed=21)
+    codes[5, :] = 255; codes[300:320, :] = 255                 # S columns without entries
+    tab = gen.codebook()
+    dev = upload(O.copyform(codes, n, k, k, tab, 255, True))
+    for m, lda, ldc in ((1, k, n), (3, k + 4, n + 3), (40, k, n + 4), (130, k + 8, n)):
+        a = gen.dense_uniform((m, lda), 3 + m); c0 = gen.dense_uniform((m, ldc), 4 + m)
+        c0[0, 5] = -0.0; c0[0, 6] = -0.0
+        for alpha, beta in ((1.0, 1.0), (1.3, 2.0), (0.7, 0.0)):
+            want = dev.addmatmat_host(a, m, lda, c0.copy(), ldc, alpha, beta)
+            for rep in range(2):                                # second call: side buffer reused
+                pa = torch.from_numpy(a.copy()).pin_memory(); pc = torch.from_numpy(c0.copy()).pin_memory()
+                dev.addmatmat_host(pa, m, lda, pc, ldc, alpha, beta)
+                assert_bits_equal(pc.numpy(), want, f"pinned vs pageable m={m} alpha={alpha} beta={beta} rep={rep}")
+    # k large enough that m = 300 is cut into slices (copies in / products / copies out pipelined)
+    n2, k2 = 520, 9000
+    codes2 = gen.codes_bernoulli(n2, k2, 0.02, seed=22)
+    dev2 = upload(O.copyform(codes2, n2, k2, k2, tab, 255, True))
+    m = 300
+    a = gen.dense_uniform((m, k2), 5); c0 = gen.dense_uniform((m, n2 + 4), 6)
+    want = dev2.addmatmat_host(a, m, k2, c0.copy(), n2 + 4, 1.3, 2.0)
+    pa = torch.from_numpy(a).pin_memory(); pc = torch.from_numpy(c0.copy()).pin_memory()
+    dev2.addmatmat_host(pa, m, k2, pc, n2 + 4, 1.3, 2.0)
+    assert_bits_equal(pc.numpy(), want, "sliced pinned path vs pageable")
+    # unaligned pinned C (scalar combine) after a larger call (side buffer larger than needed)
+    m = 5
+    a = gen.dense_uniform((m, k), 9); c0 = gen.dense_uniform((m * n + 1,), 10)
+    want = dev.addmatmat_host(a, m, k, c0[1:].copy(), n, 1.0, 1.0)
+    pc = torch.from_numpy(c0.copy()).pin_memory()
+    dev.addmatmat_host(torch.from_numpy(a).pin_memory(), m, k, pc[1:], n, 1.0, 1.0)
+    assert_bits_equal(pc[1:].numpy(), want, "unaligned pinned C")
+    assert pc[0].item() == c0[0]

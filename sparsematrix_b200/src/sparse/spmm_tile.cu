@@ -70,7 +70,16 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
     bulk_g2s_addr(smem_u32(dst), src, bytes, bar);
 }
 
-constexpr int kMaxRows = 128;                                   // W rows per CTA at most
+#ifndef TILE_MAX_ROWS
+#define TILE_MAX_ROWS 128
+#endif
+#ifndef TILE_MAXNREG_BIG
+#define TILE_MAXNREG_BIG 112
+#endif
+#ifndef TILE_MAXW_BIG
+#define TILE_MAXW_BIG 16
+#endif
+constexpr int kMaxRows = TILE_MAX_ROWS;                                   // W rows per CTA at most
 
 #ifdef EXP_TIMELINE
 __device__ unsigned long long g_timeline[2048 * 8];
@@ -79,7 +88,7 @@ __device__ __forceinline__ unsigned long long gtime() {
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     return t;
 }
-#define TL(p) do { if (threadIdx.x == 0) g_timeline[(blockIdx.y * gridDim.x + blockIdx.x) * 8 + (p)] = gtime(); } while (0)
+#define TL(p) do { if (threadIdx.x == 0) g_timeline[blockIdx.x * 8 + (p)] = gtime(); } while (0)
 #else
 #define TL(p) do { } while (0)
 #endif
@@ -181,7 +190,7 @@ transpose_in_tiled_kernel(const float *__restrict__ a, int m, int k, int lda, fl
 // blockDim.x = (nwarps + 1) * 32: nwarps consumer warps and one producer warp (the last).
 // RS = W rows per slot (a warp owns 4*RS rows).
 template <int RS, int NF4, int STAGES, bool SCALE>
-__global__ void __maxnreg__((RS == 1 && NF4 == 1) ? 64 : 112)
+__global__ void __maxnreg__((RS == 1 && NF4 == 1) ? 64 : TILE_MAXNREG_BIG)
 spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__ grp_ptr,
                  const uint32_t *__restrict__ grp_nq, const int32_t *__restrict__ row_ptr, int ngroups, int nchunks,
                  int n, const float *__restrict__ xt, int k_alloc, float *__restrict__ c, int ldc, int m, float alpha,
@@ -199,9 +208,13 @@ spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int slot = lane >> 3, c8 = lane & 7;
     const int RB = nwarps * G;
-    const int j0 = blockIdx.x * RB;
-    const int m0 = blockIdx.y * MT;
-    const float *xt_tile = xt + (size_t)blockIdx.y * k_alloc * MT;
+    // 1-D grid, m-tile fastest: the CTAs that share a block of W rows are neighbours in launch order,
+    // so the quad rows are read from HBM once and served from L2 to the other m-tiles
+    const int mtiles = (m + MT - 1) / MT;
+    const int row_block = blockIdx.x / mtiles, m_tile = blockIdx.x - row_block * mtiles;
+    const int j0 = row_block * RB;
+    const int m0 = m_tile * MT;
+    const float *xt_tile = xt + (size_t)m_tile * k_alloc * MT;
 
     TL(0);
     if (threadIdx.x == 0) {
@@ -211,13 +224,13 @@ spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__
     // Cold-start loads that nothing depends on yet: the warp's stream position, the quad-row counts
     // of every (warp, chunk) of this CTA (one contiguous piece of grp_nq), the row lengths of the
     // epilogue (kept in a register until then) and L2 prefetches of the C tile updated at the end.
-    const int g = blockIdx.x * nwarps + warp;
+    const int g = row_block * nwarps + warp;
     const bool live = warp < nwarps && g < ngroups;
     const int64_t s0 = live ? grp_ptr[(int64_t)g * nchunks] : 0;
     int my_len = 0;
     if (threadIdx.x < RB && j0 + threadIdx.x < n) my_len = row_ptr[j0 + threadIdx.x + 1] - row_ptr[j0 + threadIdx.x];
     {
-        const int64_t first = (int64_t)blockIdx.x * nwarps * nchunks, limit = (int64_t)ngroups * nchunks;
+        const int64_t first = (int64_t)row_block * nwarps * nchunks, limit = (int64_t)ngroups * nchunks;
         for (int idx = threadIdx.x; idx < nwarps * nchunks; idx += blockDim.x)
             s_nq[idx] = first + idx < limit ? grp_nq[first + idx] : 0u;
         const int lines = (RB + 31) / 32 + 1;                    // 128-byte lines of one C row segment
@@ -403,9 +416,9 @@ static int launch_tile(const sblas_b200_matrix *mat, const TileFormat &tf, const
         SB_CUDA(cudaFuncSetAttribute(spmm_tile_kernel<RS, NF4, STAGES, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
         configured = true;
     }
-    const dim3 grid((tf.ngroups + nwarps - 1) / nwarps, (m + MT - 1) / MT);
+    const dim3 grid(((tf.ngroups + nwarps - 1) / nwarps) * ((m + MT - 1) / MT));
 #ifdef EXP_TIMELINE
-    { static bool reg = false; if (!reg) { atexit(dump_timeline); reg = true; } g_tl_ctas = grid.x * grid.y; }
+    { static bool reg = false; if (!reg) { atexit(dump_timeline); reg = true; } g_tl_ctas = grid.x; }
 #endif
     // Programmatic dependent launch: this kernel may start while the transpose before it in the stream
     // is still draining; only the producer warp's X copies wait for it (griddepcontrol.wait).
@@ -446,7 +459,7 @@ TilePlan plan_tile(const sblas_b200_matrix *mat, int m, int sms) {
     for (int rs = 1; rs <= 2; ++rs)
         for (int nf4 = 1; nf4 <= 2; ++nf4) {
             if (nf4 == 2 && m <= 32) continue;
-            const int max_w = (rs == 1 && nf4 == 1) ? 28 : 16;
+            const int max_w = (rs == 1 && nf4 == 1) ? 28 : TILE_MAXW_BIG;
             const double instr = nf4 == 1 ? 38.0 : 55.0, lat = nf4 == 1 ? 90.0 : 110.0;
             const int mtiles = (m + 32 * nf4 - 1) / (32 * nf4);
             const int ngroups = (mat->n + 4 * rs - 1) / (4 * rs);
@@ -474,7 +487,7 @@ int run_spmm_tile(sblas_b200_matrix *mat, const float *d_a, int m, int lda, floa
         if ((env[0] == '1' || env[0] == '2') && (env[1] == '1' || env[1] == '2') && env[2] && env[3]) {
             plan.rs = env[0] - '0';
             plan.nf4 = env[1] - '0';
-            plan.nwarps = std::min((plan.rs == 1 && plan.nf4 == 1) ? 28 : 16, std::max(1, atoi(env + 2)));
+            plan.nwarps = std::min((plan.rs == 1 && plan.nf4 == 1) ? 28 : TILE_MAXW_BIG, std::max(1, atoi(env + 2)));
         }
     }
     TileFormat &tf = mat->tile[plan.rs == 2];

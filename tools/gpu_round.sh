@@ -1,6 +1,6 @@
 #!/bin/bash
 # One gpurun call: GPU parity tests, the C++ harness, bench lines for every config, the reference arm,
-# an ncu launch list and one --set full capture of the dominant kernel of the default bench.
+# and an ncu launch list of the default bench (full captures: tools/gpu_ncu.sh, one per gpurun call).
 # Usage (from the repo root, under gpurun):  bash tools/gpu_round.sh [tag]
 TAG=${1:-r01}
 OUT=gpurun_out/$TAG
@@ -16,9 +16,4 @@ python bench.py --impl reference --steps 5 --warmup 3 > $OUT/bench_ref_cfg2.json
 CMD="python bench.py --steps 5 --warmup 3 --no-cpu-baseline"
 $CMD > $OUT/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file $OUT/launches_cfg2.csv $CMD > $OUT/ncu_launches.log 2>&1
-$CMD > $OUT/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:spmm_tile_kernel -s 3 -c 2 -o $OUT/prof_cfg2_spmm_tile $CMD > $OUT/ncu_full.log 2>&1
-CMD4="python bench.py --workload cfg4 --steps 5 --warmup 3 --no-cpu-baseline"
-$CMD4 > $OUT/plain4.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:spmv_rows_kernel -s 3 -c 2 -o $OUT/prof_cfg4_spmv $CMD4 > $OUT/ncu_full4.log 2>&1
 tail -3 $OUT/pytest_gpu.log; cat $OUT/bench_cfg2.json

@@ -123,6 +123,31 @@ SBLAS_B200_API int sblas_b200_upload_csr(const int32_t *row_ptr, const int32_t *
 SBLAS_B200_API int sblas_b200_partition(const int32_t *block_bounds, const int32_t *block_index_bounds,
                                         int32_t nblocks, int32_t cols, int32_t parts, int32_t *col_splits);
 
+/*
+ * CopyForm on the device (reference src/sparse/sparse-matrix.cc:21-99): dense
+ * code matrix -> the reference's byte streams, bit for bit (fillers, per-panel
+ * restart of the position, empty panels not recorded), and from them the device
+ * layout without a host round trip.  Two calls because the caller owns the
+ * output arrays and their sizes are a result:
+ *   _begin  : codes is rows x stride bytes (host or device pointer), a code
+ *             < valid_table_size is an element, anything else is a zero; trans != 0
+ *             means the input is S^T (SblasTrans).  Returns the job, the number
+ *             of stream entries and of recorded panels.
+ *   _finish : writes pos_index/val_index (entries bytes each), block_bounds and
+ *             block_index_bounds (nblocks pairs each) to HOST arrays; when `mat`
+ *             is not NULL also builds the device matrix (val_table: valid_table_size
+ *             floats) as sblas_b200_upload would.  Frees the job in every case.
+ *   _abort  : frees a job that will not be finished.
+ */
+typedef struct sblas_b200_copyform_job sblas_b200_copyform_job;
+SBLAS_B200_API int sblas_b200_copyform_begin(const uint8_t *codes, int32_t rows, int32_t cols, int32_t stride,
+                                             int32_t valid_table_size, int32_t trans, int32_t device,
+                                             sblas_b200_copyform_job **job, int64_t *entries, int32_t *nblocks);
+SBLAS_B200_API int sblas_b200_copyform_finish(sblas_b200_copyform_job *job, uint8_t *pos_index, uint8_t *val_index,
+                                              int32_t *block_bounds, int32_t *block_index_bounds,
+                                              const float *val_table, sblas_b200_matrix **mat);
+SBLAS_B200_API void sblas_b200_copyform_abort(sblas_b200_copyform_job *job);
+
 SBLAS_B200_API int sblas_b200_free(sblas_b200_matrix *mat);
 SBLAS_B200_API int sblas_b200_get_info(const sblas_b200_matrix *mat, sblas_b200_info *info);
 

@@ -48,6 +48,9 @@ SYMBOLS = {
     "sblas_b200_profile_end": (C.c_int, [_vp, _vp, _vp]),
     "sblas_b200_decode_dense": (C.c_int, [_vp, _vp, _i32, _i32]),
     "sblas_b200_export_csr": (C.c_int, [_vp, _vp, _vp, _vp]),
+    "sblas_b200_copyform_begin": (C.c_int, [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _vp, _vp]),
+    "sblas_b200_copyform_finish": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "sblas_b200_copyform_abort": (None, [_vp]),
     # sblas_b200_host.h
     "sblas_host_create": (_vp, []),
     "sblas_host_free": (None, [_vp]),

@@ -139,6 +139,25 @@ class DeviceMatrix:
         return row_ptr, col, code
 
 
+def copyform_device(codes, rows, cols, stride, vals, T, trans=False, device=0, want_matrix=True):
+    """sblas_b200_copyform_begin/_finish: CopyForm on the device (reference sparse-matrix.cc:21-99).
+    codes: uint8 host array (rows x stride) or a torch CUDA tensor.
+    -> (pos, code, block_bounds[nb,2], block_index_bounds[nb,2], DeviceMatrix or None)"""
+    L = _capi.lib()
+    if isinstance(codes, np.ndarray):
+        codes = np.ascontiguousarray(codes, np.uint8).reshape(-1)
+    vals = np.ascontiguousarray(vals, np.float32).reshape(-1)
+    job = C.c_void_p(); entries = C.c_int64(0); nb = C.c_int32(0)
+    _capi.check(L.sblas_b200_copyform_begin(_ptr(codes), rows, cols, stride, T, int(bool(trans)), device,
+                                            C.byref(job), C.byref(entries), C.byref(nb)))
+    pos = np.empty(entries.value, np.uint8); code = np.empty(entries.value, np.uint8)
+    bb = np.zeros((nb.value, 2), np.int32); bib = np.zeros((nb.value, 2), np.int32)
+    h = C.c_void_p()
+    _capi.check(L.sblas_b200_copyform_finish(job, _ptr(pos), _ptr(code), _ptr(bb), _ptr(bib), _ptr(vals),
+                                             C.byref(h) if want_matrix else None))
+    return pos, code, bb, bib, (DeviceMatrix(h) if want_matrix else None)
+
+
 def partition(block_bounds, block_index_bounds, cols, parts):
     """sblas_b200_partition: nnz-balanced panel-aligned column splits, length parts+1."""
     bb = np.ascontiguousarray(block_bounds, np.int32).reshape(-1, 2)

@@ -32,6 +32,49 @@ SBLAS_TMPL void SBLAS_CLS::Destroy() {
     rows_ = cols_ = 0;
 }
 
+// CopyForm on the device (src/utils/copyform.cu) for inputs large enough to pay for the trip:
+// fills the members with exactly the bytes the scan below produces and registers the device
+// matrix built from the device-resident streams, so the first AddMatMat uploads nothing.
+// SBLAS_B200_COPYFORM=host|device forces one side (default: device from 2^18 elements).
+template <typename Owner>
+static bool DeviceCopyForm(Owner *owner, const uint8_t *codes, int32 rows, int32 cols, int32 stride, int32 T, bool trans,
+                           const std::vector<float> &val_table, std::vector<uint8_t> *pos, std::vector<uint8_t> *val,
+                           std::vector<std::pair<int32, int32> > *bounds, std::vector<std::pair<int32, int32> > *index_bounds) {
+    const char *env = getenv("SBLAS_B200_COPYFORM");
+    if (env && env[0] == 'h') return false;
+    if (!(env && env[0] == 'd') && (int64_t)rows * cols < (1 << 18)) return false;
+    const int dev = device::CurrentDevice();
+    if (dev < 0) return false;
+    sblas_b200_copyform_job *job = nullptr;
+    int64_t entries = 0;
+    int32 nblocks = 0;
+    int rc = sblas_b200_copyform_begin(codes, rows, cols, stride, T, trans ? 1 : 0, dev, &job, &entries, &nblocks);
+    if (rc != SBLAS_B200_OK) {
+        printf("CopyForm: device path unavailable (%d: %s), scanning on the host\n", rc, sblas_b200_last_error());
+        return false;
+    }
+    pos->resize((size_t)entries);
+    val->resize((size_t)entries);
+    bounds->resize((size_t)nblocks);
+    index_bounds->resize((size_t)nblocks);
+    sblas_b200_matrix *mat = nullptr;
+    rc = sblas_b200_copyform_finish(job, pos->data(), val->data(), nblocks ? &(*bounds)[0].first : nullptr,
+                                    nblocks ? &(*index_bounds)[0].first : nullptr, val_table.data(), &mat);
+    if (rc != SBLAS_B200_OK) {
+        printf("CopyForm: device path failed (%d: %s), scanning on the host\n", rc, sblas_b200_last_error());
+        pos->clear(); val->clear(); bounds->clear(); index_bounds->clear();
+        return false;
+    }
+    device::Adopt(owner, dev, mat);
+    return true;
+}
+
+template <typename Owner, typename P, typename V, typename F>
+static bool DeviceCopyForm(Owner *, const V *, int32, int32, int32, int32, bool, const std::vector<F> &, std::vector<P> *,
+                           std::vector<V> *, std::vector<std::pair<int32, int32> > *, std::vector<std::pair<int32, int32> > *) {
+    return false;                                   // other instantiations: host scan only
+}
+
 // One pass over S in panel order.  S(r, j) is read through `at`, which hides the
 // orientation of the dense input; everything else is orientation independent.
 SBLAS_TMPL void SBLAS_CLS::CopyForm(const ValIndex_t *density_matrix, int32 rows, int32 cols, int32 stride,
@@ -50,6 +93,13 @@ SBLAS_TMPL void SBLAS_CLS::CopyForm(const ValIndex_t *density_matrix, int32 rows
 
     val_table_.assign(vals, vals + val_table_size);
     val_table_.push_back(Value_t(0));                                              // trailing zero entry
+
+    if (DeviceCopyForm(this, density_matrix, rows, cols, stride, val_table_size, t, val_table_, &pos_index_, &val_index_,
+                       &block_bounds_, &block_index_bounds_)) {
+        rows_ = s_rows;
+        cols_ = s_cols;
+        return;
+    }
 
     for (int32 j0 = 0; j0 < s_cols; j0 += panel_w) {
         const int32 width = (s_cols - j0 < panel_w) ? s_cols - j0 : panel_w;

@@ -495,8 +495,8 @@ static int upload_stream_impl(const uint8_t *pos_index, const uint8_t *val_index
     if (nseg) {
         SB_CUDA(cudaMalloc((void **)&sc.pos, (size_t)mat->entries));
         SB_CUDA(cudaMalloc((void **)&sc.code, (size_t)mat->entries));
-        SB_CUDA(cudaMemcpy(sc.pos, pos_index + e_begin, (size_t)mat->entries, cudaMemcpyHostToDevice));
-        SB_CUDA(cudaMemcpy(sc.code, val_index + e_begin, (size_t)mat->entries, cudaMemcpyHostToDevice));
+        SB_CUDA(cudaMemcpy(sc.pos, pos_index + e_begin, (size_t)mat->entries, cudaMemcpyDefault));   // host streams, or the device-resident ones of copyform.cu
+        SB_CUDA(cudaMemcpy(sc.code, val_index + e_begin, (size_t)mat->entries, cudaMemcpyDefault));
         SB_CUDA(cudaMalloc((void **)&sc.seg_begin, (size_t)nseg * 4));
         SB_CUDA(cudaMalloc((void **)&sc.seg_end, (size_t)nseg * 4));
         SB_CUDA(cudaMalloc((void **)&sc.seg_panel, (size_t)nseg * 4));

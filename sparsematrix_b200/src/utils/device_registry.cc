@@ -42,6 +42,20 @@ sblas_b200_matrix *Acquire(const void *owner, const StreamView &v) {
     return mat;
 }
 
+void Adopt(const void *owner, int dev, sblas_b200_matrix *mat) {
+    std::lock_guard<std::mutex> guard(g_lock);
+    auto key = std::make_pair(owner, dev);
+    auto it = table().find(key);
+    if (it != table().end()) sblas_b200_free(it->second);
+    table()[key] = mat;
+}
+
+int CurrentDevice() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return -1; }
+    return dev;
+}
+
 void Evict(const void *owner) {
     std::lock_guard<std::mutex> guard(g_lock);
     auto &t = table();

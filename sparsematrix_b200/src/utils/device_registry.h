@@ -30,6 +30,13 @@ struct StreamView {                 // the compressed members, as plain pointers
 // Returns nullptr after printing the library's error message.
 sblas_b200_matrix *Acquire(const void *owner, const StreamView &view);
 
+// Register a device matrix built elsewhere (device CopyForm) for `owner` on device `dev`; the
+// registry owns it from here on.  An existing entry is freed first.
+void Adopt(const void *owner, int dev, sblas_b200_matrix *mat);
+
+// Ordinal of the current CUDA device, -1 when there is none.
+int CurrentDevice();
+
 // Drop and free whatever is registered for `owner` (no-op when nothing is).
 void Evict(const void *owner);
 

@@ -337,3 +337,74 @@ def test_pinned_host_buffers_give_the_same_bits_as_pageable_ones():
     dev.addmatmat_host(torch.from_numpy(a).pin_memory(), m, k, pc[1:], n, 1.0, 1.0)
     assert_bits_equal(pc[1:].numpy(), want, "unaligned pinned C")
     assert pc[0].item() == c0[0]
+
+
+# ------------------------------------------------------------------ CopyForm on the device
+def _assert_same_streams(pos, code, bb, bib, s, what):
+    assert pos.shape[0] == s.entries, (what, pos.shape[0], s.entries)
+    assert np.array_equal(pos, s.pos), what + ": pos_index"
+    assert np.array_equal(code, s.code), what + ": val_index"
+    assert np.array_equal(bb, s.block_bounds.reshape(-1, 2)), what + ": block_bounds"
+    assert np.array_equal(bib, s.block_index_bounds.reshape(-1, 2)), what + ": block_index_bounds"
+
+
+@pytest.mark.parametrize("rows,cols,stride,dens,T,trans", [
+    (3, 2, 2, 0.5, 8, False),                  # SelfTest size
+    (1023, 511, 512, 0.25, 63, False),         # SelfTest round trip shape, narrow last panel
+    (1023, 511, 512, 0.25, 63, True),
+    (777, 1000, 1003, 0.04, 255, True),        # odd stride, several panels
+    (600, 2000, 2000, 0.001, 255, False),      # hypersparse: long filler runs, empty panels
+    (600, 2000, 2000, 0.001, 255, True),
+    (257, 513, 520, 1.0, 200, False),          # fully dense, codes >= T count as zeros
+    (4096, 300, 300, 0.10, 255, True),
+    (40, 70000, 70000, 0.0005, 17, False),     # many panels, most of them empty
+])
+def test_device_copyform_streams_are_bit_identical(rows, cols, stride, dens, T, trans):
+    rng = np.random.default_rng(rows * 31 + cols)
+    codes = np.full((rows, stride), 255, np.uint8)
+    mask = rng.random((rows, cols)) < dens
+    vals = rng.integers(0, 256 if dens == 1.0 else T, size=(rows, cols)).astype(np.uint8)
+    codes[:, :cols][mask] = vals[mask]
+    tab = gen.codebook(T, 1)
+    s = O.copyform(codes, rows, cols, stride, tab, T, trans)
+    pos, code, bb, bib, dev = sb.copyform_device(codes, rows, cols, stride, tab, T, trans)
+    _assert_same_streams(pos, code, bb, bib, s, "device CopyForm vs oracle")
+    # the device matrix built from the device-resident streams = the one uploaded from host streams
+    ref = upload(s)
+    for x, y in zip(dev.export_csr(), ref.export_csr()):
+        assert np.array_equal(x, y)
+    assert dev.info().fillers == ref.info().fillers
+
+
+def test_device_copyform_edge_cases_and_host_class_route():
+    import os
+    tab = gen.codebook(255, 1)
+    # nothing valid at all -> no entries, no panels; T = 0 -> empty object
+    codes = np.full((50, 300), 255, np.uint8)
+    pos, code, bb, bib, dev = sb.copyform_device(codes, 50, 300, 300, tab, 255, False)
+    assert pos.shape[0] == 0 and bb.shape[0] == 0 and dev.nnz == 0
+    pos, code, bb, bib, dev = sb.copyform_device(codes, 50, 300, 300, tab, 0, True)
+    assert pos.shape[0] == 0 and bb.shape[0] == 0
+    # single element at the far corner: one long filler run
+    codes[49, 299] = 3
+    s = O.copyform(codes, 50, 300, 300, tab, 255, False)
+    pos, code, bb, bib, dev = sb.copyform_device(codes, 50, 300, 300, tab, 255, False)
+    _assert_same_streams(pos, code, bb, bib, s, "corner element")
+    # the host class takes the device route for large inputs (and when forced) and ends up equal to the host scan
+    n, k = 700, 900
+    big = gen.codes_bernoulli(n, k, 0.05, seed=31)
+    a = gen.dense_uniform((5, k), 1); c0 = gen.dense_uniform((5, n), 2)
+    old = os.environ.get("SBLAS_B200_COPYFORM")
+    try:
+        os.environ["SBLAS_B200_COPYFORM"] = "host"
+        H = sb.SparseMatrix(big, n, k, k, tab, 255, sb.SparseMatrix.Trans)
+        os.environ["SBLAS_B200_COPYFORM"] = "device"
+        D = sb.SparseMatrix(big, n, k, k, tab, 255, sb.SparseMatrix.Trans)
+    finally:
+        if old is None: os.environ.pop("SBLAS_B200_COPYFORM", None)
+        else: os.environ["SBLAS_B200_COPYFORM"] = old
+    assert H == D
+    for x, y in zip(H.members(), D.members()):
+        assert np.array_equal(np.asarray(x), np.asarray(y))
+    assert_bits_equal(D.AddMatMat(a, 5, k, c0.copy(), n, 1.3, 2.0), H.AddMatMat(a, 5, k, c0.copy(), n, 1.3, 2.0), "device-built vs host-built object")
+    assert np.array_equal(D.CopyTo(n, sb.SparseMatrix.Trans), H.CopyTo(n, sb.SparseMatrix.Trans))

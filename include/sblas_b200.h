@@ -185,8 +185,9 @@ SBLAS_B200_API int sblas_b200_profile_end(sblas_b200_matrix *mat, double *total_
 
 /* ---- structure read-back (parity tests) --------------------------------- */
 /*
- * Decode on the device and copy to the host: the function of CopyTo
- * (sparse-matrix.cc:101-137) for the columns this handle holds.
+ * Decode on the device: the function of CopyTo (sparse-matrix.cc:101-137) for
+ * the columns this handle holds.  `dense` is a host pointer (decoded into a
+ * staging buffer and copied out) or a device pointer (decoded in place).
  *   trans == 0 : dense is s_rows x stride, dense[r*stride + j] = S(r, col_begin + j)
  *   trans == 1 : dense is s_cols x stride, dense[j*stride + r] = S(r, col_begin + j)
  * The whole leading x stride area is cleared first, like the reference's memset.

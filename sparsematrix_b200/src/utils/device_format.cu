@@ -724,17 +724,20 @@ int sblas_b200_decode_dense(const sblas_b200_matrix *mat, float *dense, int32_t 
     if (lead == 0 || stride == 0) return SBLAS_B200_OK;
     DeviceScope scope(mat->device);
     if (!scope.ok()) return SBLAS_B200_ECUDA;
-    float *d_dense = nullptr;
     const size_t bytes = (size_t)lead * stride * 4;
-    SB_CUDA(cudaMalloc((void **)&d_dense, bytes));
+    cudaPointerAttributes attr;
+    const bool on_device = cudaPointerGetAttributes(&attr, dense) == cudaSuccess && attr.type == cudaMemoryTypeDevice;
+    cudaGetLastError();
+    float *d_dense = on_device ? dense : nullptr;                  // device caller: decode in place, no staging
+    if (!on_device) SB_CUDA(cudaMalloc((void **)&d_dense, bytes));
     cudaError_t e = cudaMemset(d_dense, 0, bytes);                 // memset(density_matrix, 0, ...) sparse-matrix.cc:109,123
     if (e == cudaSuccess && mat->n) {
         SB_LAUNCH(decode_dense_kernel, (mat->n + 7) / 8, 256, 0, 0, mat->d_row_ptr, mat->d_col, mat->d_code, mat->d_table,
                   mat->n, d_dense, stride, trans);
         e = cudaGetLastError();
     }
-    if (e == cudaSuccess) e = cudaMemcpy(dense, d_dense, bytes, cudaMemcpyDeviceToHost);
-    cudaFree(d_dense);
+    if (e == cudaSuccess) e = on_device ? cudaDeviceSynchronize() : cudaMemcpy(dense, d_dense, bytes, cudaMemcpyDeviceToHost);
+    if (!on_device) cudaFree(d_dense);
     if (e != cudaSuccess) return cuda_fail(e, "decode_dense", __FILE__, __LINE__);
     return SBLAS_B200_OK;
 }

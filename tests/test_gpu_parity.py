@@ -408,3 +408,16 @@ def test_device_copyform_edge_cases_and_host_class_route():
         assert np.array_equal(np.asarray(x), np.asarray(y))
     assert_bits_equal(D.AddMatMat(a, 5, k, c0.copy(), n, 1.3, 2.0), H.AddMatMat(a, 5, k, c0.copy(), n, 1.3, 2.0), "device-built vs host-built object")
     assert np.array_equal(D.CopyTo(n, sb.SparseMatrix.Trans), H.CopyTo(n, sb.SparseMatrix.Trans))
+
+
+def test_decode_dense_into_device_memory():
+    import torch
+    n, k = 300, 500
+    codes = gen.codes_bernoulli(n, k, 0.05, seed=33)
+    tab = gen.codebook()
+    dev = upload(O.copyform(codes, n, k, k, tab, 255, True))
+    for trans, shape in ((False, (k, n + 5)), (True, (n, k + 3))):
+        want = dev.decode_dense(shape[1], trans)
+        d = torch.full(shape, 7.0, dtype=torch.float32, device="cuda")
+        _capi.check(sb.lib().sblas_b200_decode_dense(dev._h, C.c_void_p(d.data_ptr()), shape[1], int(trans)))
+        assert np.array_equal(d.cpu().numpy(), want)

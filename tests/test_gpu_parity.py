@@ -421,3 +421,63 @@ def test_decode_dense_into_device_memory():
         d = torch.full(shape, 7.0, dtype=torch.float32, device="cuda")
         _capi.check(sb.lib().sblas_b200_decode_dense(dev._h, C.c_void_p(d.data_ptr()), shape[1], int(trans)))
         assert np.array_equal(d.cpu().numpy(), want)
+
+
+# ------------------------------------------------------------------ every template instance, forced through the experiment switches
+def _with_env(name, value, fn):
+    import os
+    old = os.environ.get(name)
+    os.environ[name] = value
+    try:
+        return fn()
+    finally:
+        if old is None: os.environ.pop(name, None)
+        else: os.environ[name] = old
+
+
+def test_every_spmm_tile_variant_gives_the_same_bits():
+    """rows per slot x float4s per lane x warps: every row is summed by one slot in column order,
+    so all instances of spmm_tile_kernel must agree bit for bit, and with the fp64 statement to TOL."""
+    n, k = 610, 1300                                           # 6 chunks of 255 X rows, ragged last group
+    codes = gen.codes_bernoulli(n, k, 0.08, seed=41)
+    codes[7, :] = 255; codes[100:109, :] = 255                 # empty W rows
+    codes[300, :] = (np.arange(k) % 200).astype(np.uint8)      # one dense row
+    tab = gen.codebook()
+    s = O.copyform(codes, n, k, k, tab, 255, True)
+    dev = upload(s)
+    for m, lda, ldc, alpha, beta in ((17, k, n, 1.0, 1.0), (40, k + 4, n + 3, 1.3, 2.0), (100, k, n, 0.7, 0.0)):
+        a = gen.dense_uniform((m, lda), 50 + m); c0 = gen.dense_uniform((m, ldc), 60 + m)
+        y64, bound = O.addmatmat_f64(s, a, m, lda, c0, ldc, alpha, beta)
+        first = None
+        for variant in ("1104", "1128", "1204", "1216", "2103", "2116", "2204", "2216"):
+            got = _with_env("SBLAS_B200_TILE", variant, lambda: dev.addmatmat_host(a, m, lda, c0.copy(), ldc, alpha, beta))
+            back = O.error_measures(got, m, n, ldc, y64, bound)[0]
+            assert back <= TOL, (variant, m, back)
+            if first is None: first = got
+            else: assert_bits_equal(got, first, f"tile variant {variant} vs 1104, m={m}")
+
+
+def test_every_spmv_width_and_the_sorted_copy():
+    n, k = 70000, 3000                                         # >= 65536 rows so the sorted copy can be forced
+    row_ptr, col, code = gen.powerlaw_csr(n, k, seed=42, x_min=2, cap=2500)
+    lens = np.diff(row_ptr).astype(np.int64)                   # rows 10..19 and the last one lose their entries
+    keep = np.ones(col.shape[0], bool)
+    keep[row_ptr[10]:row_ptr[20]] = False; keep[row_ptr[n - 1]:] = False
+    lens[10:20] = 0; lens[n - 1] = 0
+    col, code = col[keep], code[keep]
+    row_ptr = np.concatenate(([0], np.cumsum(lens))).astype(np.int32)
+    tab = gen.codebook()
+    a = gen.dense_uniform((1, k), 1); c0 = gen.dense_uniform((1, n), 2)
+    y64, bound = O.addmatmat_csr_f64(row_ptr, col, code, tab, 255, n, k, a, 1, k, c0, n, 1.3, 2.0)
+    for sort_rows in ("0", "1"):
+        for lanes in ("1", "2", "4", "8", "16", "32"):
+            dev = _with_env("SBLAS_B200_SORT_ROWS", sort_rows, lambda: _with_env(
+                "SBLAS_B200_SPMV_LANES", lanes, lambda: sb.DeviceMatrix.upload_csr(row_ptr, col, code, tab, 255, n, k)))
+            assert dev.info().spmv_lanes == int(lanes)
+            got = dev.addmatmat_host(a, 1, k, c0.copy(), n, 1.3, 2.0)
+            back = O.error_measures(got, 1, n, n, y64, bound)[0]
+            assert back <= TOL, (sort_rows, lanes, back)
+            # rows without entries keep exactly beta*c
+            empty = np.flatnonzero(np.diff(row_ptr) == 0)
+            if empty.size:
+                assert np.array_equal(got.reshape(-1)[empty], (np.float32(2.0) * c0.reshape(-1)[empty]))

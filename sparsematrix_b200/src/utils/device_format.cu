@@ -327,7 +327,9 @@ int plan_spmv(sblas_b200_matrix *mat, const int32_t *h_row_ptr) {
         if (v == 1 || v == 2 || v == 4 || v == 8 || v == 16 || v == 32) lanes = v;
     }
     mat->spmv_lanes = lanes;
-    mat->long_threshold = std::max(1024, 256 * lanes);
+    // a sub-warp streams rows up to 512 entries per lane; at 256 per lane the 16384^2 / 50 % case had half
+    // of its rows (about 8192 entries) on the split-row path and ran 207 instead of 158 us
+    mat->long_threshold = std::max(1024, 512 * lanes);
     if (const char *env = getenv("SBLAS_B200_LONG_THRESHOLD")) {
         const int v = atoi(env);
         if (v > 0) mat->long_threshold = v;

@@ -481,3 +481,30 @@ def test_every_spmv_width_and_the_sorted_copy():
             empty = np.flatnonzero(np.diff(row_ptr) == 0)
             if empty.size:
                 assert np.array_equal(got.reshape(-1)[empty], (np.float32(2.0) * c0.reshape(-1)[empty]))
+
+
+def test_long_row_spmv_full_warp_per_row():
+    """Mean row length >= 128 selects a full warp per row: rows of exactly 128 / 129 entries, a full-width
+    row, an empty row and a single-entry last row."""
+    n, k = 333, 5000
+    codes = gen.codes_bernoulli(n, k, 0.30, seed=51)
+    codes[3, :] = 255                                          # empty row
+    codes[4, :] = 255; codes[4, :128] = 7                      # exactly one full record
+    codes[5, :] = 255; codes[5, :129] = 9                      # one full record + 1 entry
+    codes[6, :] = (np.arange(k) % 250).astype(np.uint8)        # every column: 40 records
+    codes[n - 1, :] = 255; codes[n - 1, k - 1] = 1             # single entry in the last row
+    tab = gen.codebook()
+    s = O.copyform(codes, n, k, k, tab, 255, True)
+    dev = upload(s)
+    assert dev.info().spmv_lanes == 32
+    a = gen.dense_uniform((1, k), 1); c0 = gen.dense_uniform((1, n), 2); c0[0, 3] = -0.0
+    for alpha, beta in ((1.0, 1.0), (1.3, 2.0), (0.7, 0.0)):
+        got = dev.addmatmat_host(a, 1, k, c0.copy(), n, alpha, beta)
+        y64, bound = O.addmatmat_f64(s, a, 1, k, c0, n, alpha, beta)
+        back = O.error_measures(got, 1, n, n, y64, bound)[0]
+        want = O.addmatmat(s, a, 1, k, c0.copy(), n, alpha, beta)
+        assert back <= TOL, (alpha, beta, back)
+        assert got.reshape(-1)[3].tobytes() == want.reshape(-1)[3].tobytes()       # empty row: exactly beta*c (keeps -0)
+        got2 = dev.addmatmat_host(a, 1, k, c0.copy(), n, alpha, beta)
+        assert_bits_equal(got, got2, "run-to-run determinism")
+    assert dev.info().device_bytes > 0

@@ -44,24 +44,30 @@ def gpu_time(mat, d_a, d_c, m, k, n, flush, steps=30):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--big", action="store_true", help="also n = k = 16384 (GPU only)")
+    ap.add_argument("--m", type=int, nargs="*", default=[1, 32, 256])
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--sparsity", type=float, nargs="*", default=[50.0, 75.0, 90.0, 95.0, 99.0, 99.9])
+    ap.add_argument("--sizes", type=int, nargs="*", default=None)
     args = ap.parse_args()
     dev = torch.device("cuda", 0)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     tab = gen.codebook(255, 1)
     print("| n=k | sparsity | m | nnz | GPU cold us | GPU warm us | GPU GFLOP/s (cold) | ref CPU ms (1 thread) | CPU GFLOP/s | GPU/CPU |")
     print("|---|---|---|---|---|---|---|---|---|---|")
-    sizes = [4096] + ([16384] if args.big else [])
+    sizes = args.sizes or ([4096] + ([16384] if args.big else []))
     for n in sizes:
         for idx, sp in enumerate([50.0, 75.0, 90.0, 95.0, 99.0, 99.9]):
+            if sp not in args.sparsity:
+                continue
             codes = gen.codes_bernoulli(n, n, 1.0 - sp / 100.0, 100 + idx)
             nnz = int((codes != 255).sum())
             S = sb.SparseMatrix(codes, n, n, n, tab, 255, sb.SparseMatrix.Trans)
             mat = S.device_matrix()
             R = None
-            if n == 4096 and O.have_ref():
+            if n == 4096 and O.have_ref() and not args.no_cpu:
                 R = O.RefMatrix()
                 R.CopyForm(codes, n, n, n, tab, 255, True)
-            for m in (1, 32, 256):
+            for m in args.m:
                 a = gen.dense_uniform((m, n), 2)
                 d_a = torch.from_numpy(a).to(dev)
                 d_c = torch.zeros((m, n), dtype=torch.float32, device=dev)

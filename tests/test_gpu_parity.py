@@ -508,3 +508,32 @@ def test_long_row_spmv_full_warp_per_row():
         got2 = dev.addmatmat_host(a, 1, k, c0.copy(), n, alpha, beta)
         assert_bits_equal(got, got2, "run-to-run determinism")
     assert dev.info().device_bytes > 0
+
+
+def test_spmv_never_touches_x_where_no_entry_is():
+    """Every sub-warp width on a matrix with wide gaps, rows of 4 j and 4 j + 1 entries (block edges of the
+    128-bit column loads), empty rows; an Inf in x at a column no entry uses must not reach any result
+    (padding / masked lanes must not multiply 0 * x)."""
+    n, k = 500, 3000
+    rng = np.random.default_rng(61)
+    codes = gen.codes_bernoulli(n, k, 0.06, seed=61)
+    codes[:, 700:1400] = 255                                   # a 700-column gap in every row: 2 fillers each
+    codes[10, :] = 255                                         # empty row
+    codes[11, :] = 255; codes[11, 2990:2994] = 5               # 4 entries, first one after 11 fillers
+    codes[12, :] = 255; codes[12, 0:5] = 6                     # 5 entries from column 0
+    codes[13, :] = 255; codes[13, k - 1] = 7                   # single entry in the last column
+    codes[:, 1000] = 255                                       # column 1000 is used by no entry
+    tab = gen.codebook()
+    s = O.copyform(codes, n, k, k, tab, 255, True)
+    a = gen.dense_uniform((1, k), 1); c0 = gen.dense_uniform((1, n), 2); c0[0, 10] = -0.0
+    a_inf = a.copy(); a_inf[0, 1000] = np.inf
+    for lanes in ("1", "2", "4", "8", "16", "32"):
+        dev = _with_env("SBLAS_B200_SPMV_LANES", lanes, lambda: upload(s))
+        for alpha, beta in ((1.0, 1.0), (1.3, 2.0), (0.7, 0.0)):
+            got = dev.addmatmat_host(a, 1, k, c0.copy(), n, alpha, beta)
+            y64, bound = O.addmatmat_f64(s, a, 1, k, c0, n, alpha, beta)
+            assert O.error_measures(got, 1, n, n, y64, bound)[0] <= TOL, (lanes, alpha, beta)
+            want = O.addmatmat(s, a, 1, k, c0.copy(), n, alpha, beta)
+            assert got.reshape(-1)[10].tobytes() == want.reshape(-1)[10].tobytes()   # empty row: exactly beta*c
+            got_inf = dev.addmatmat_host(a_inf, 1, k, c0.copy(), n, alpha, beta)
+            assert_bits_equal(got_inf, got, f"Inf in an unused column of x, lanes={lanes}")

@@ -378,7 +378,8 @@ static int launch_tile(const sblas_b200_matrix *mat, const TileFormat &tf, const
     const int nchunks = tf.nchunks;
     auto smem_for = [nchunks](int nw) { return (size_t)STAGES * 256 * MT * 4 + (size_t)nw * kRingBytes + 2 * STAGES * 8 + (size_t)nw * nchunks * 4; };
     if (smem_for(nwarps) > 226 * 1024) return 1;                  // k too long for the per-chunk counts: gather kernel
-    static bool configured = false;                              // per template instance
+    static bool configured_on[64] = {false};                     // per template instance and device (the attribute is per context)
+    bool &configured = configured_on[mat->device & 63];
     if (!configured) {
         (void)MAXW;
         SB_CUDA(cudaFuncSetAttribute(spmm_tile_kernel<RS, NF4, STAGES, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));

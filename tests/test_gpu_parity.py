@@ -537,3 +537,70 @@ def test_spmv_never_touches_x_where_no_entry_is():
             assert got.reshape(-1)[10].tobytes() == want.reshape(-1)[10].tobytes()   # empty row: exactly beta*c
             got_inf = dev.addmatmat_host(a_inf, 1, k, c0.copy(), n, alpha, beta)
             assert_bits_equal(got_inf, got, f"Inf in an unused column of x, lanes={lanes}")
+
+
+# ------------------------------------------------------------------ BASELINE full sizes, checked through sampled rows and invariants
+def _sampled_backward_error(got_cols, w_rows_codes, tab, a, c0_cols, alpha, beta):
+    """got_cols: m x s outputs of the sampled W rows; w_rows_codes: s x k codes of those rows."""
+    w = np.where(w_rows_codes < 255, tab.astype(np.float64)[np.minimum(w_rows_codes, 254)], 0.0)      # s x k
+    a64 = a.astype(np.float64)
+    y64 = beta * c0_cols.astype(np.float64) + alpha * (a64 @ w.T)
+    bound = np.abs(beta * c0_cols.astype(np.float64)) + abs(alpha) * (np.abs(a64) @ np.abs(w).T)
+    return float(np.max(np.abs(got_cols.astype(np.float64) - y64) / np.maximum(bound, 1e-300)))
+
+
+def test_config3_full_size_sampled_rows_and_invariants():
+    # BASELINE.json configs[2]: 16384 x 16384 at 95 % sparsity x dense N = 512
+    import torch
+    n = k = 16384; m = 512
+    codes = gen.codes_bernoulli(n, k, 0.05, seed=13)
+    tab = gen.codebook()
+    S = sb.SparseMatrix(codes, n, k, k, tab, 255, 1)           # CopyForm takes the device route at this size
+    dev = S.device_matrix()
+    assert dev.nnz == int((codes != 255).sum())
+    a = gen.dense_uniform((m, k), 2); c0 = gen.dense_uniform((m, n), 3)
+    got = dev.addmatmat_host(a, m, k, c0.copy(), n, 1.3, 2.0)
+    rows = np.random.default_rng(5).choice(n, 48, replace=False)
+    err = _sampled_backward_error(got[:, rows], codes[rows], tab, a, c0[:, rows], 1.3, 2.0)
+    assert err <= TOL, err
+    # an output element does not depend on how many other A rows are multiplied with it (m-tile
+    # shape, kernel variant) nor on the host route (pinned, sliced copies)
+    part = dev.addmatmat_host(a[100:164], 64, k, c0[100:164].copy(), n, 1.3, 2.0)
+    assert_bits_equal(part, got[100:164], "m = 64 slice vs rows 100..163 of the m = 512 product")
+    pa = torch.from_numpy(a).pin_memory(); pc = torch.from_numpy(c0.copy()).pin_memory()
+    dev.addmatmat_host(pa, m, k, pc, n, 1.3, 2.0)
+    assert_bits_equal(pc.numpy(), got, "pinned + sliced host route at full size")
+    # row slabs (8 virtual shards) concatenate to the same bits
+    pos, code, table, T, bb, bib = S.members()
+    splits = sb.partition(bb, bib, n, 8)
+    for g in (0, 3, 7):
+        lo, hi = int(splits[g]), int(splits[g + 1])
+        slab = S.upload_slab(lo, hi)
+        cs = np.ascontiguousarray(c0[:, lo:hi])
+        ys = slab.addmatmat_host(a, m, k, cs, hi - lo, 1.3, 2.0)
+        assert_bits_equal(ys, got[:, lo:hi], f"slab {g}")
+
+
+def test_config4_full_size_sampled_rows():
+    # BASELINE.json configs[3]: power-law SpMV, 2^23 rows, ~16 nnz/row, direct CSR
+    n = k = 1 << 23
+    row_ptr, col, code = gen.powerlaw_csr(n, k, seed=14)
+    tab = gen.codebook()
+    dev = sb.DeviceMatrix.upload_csr(row_ptr, col, code, tab, 255, n, k)
+    assert dev.nnz == int(row_ptr[-1])
+    a = gen.dense_uniform((1, k), 2); c0 = gen.dense_uniform((1, n), 3)
+    got = dev.addmatmat_host(a, 1, k, c0.copy(), n, 1.3, 2.0).reshape(-1)
+    lens = np.diff(row_ptr)
+    rng = np.random.default_rng(6)
+    rows = np.concatenate([rng.choice(n, 2000, replace=False), np.argsort(lens)[-20:], np.flatnonzero(lens == lens.min())[:20]])
+    tab64 = tab.astype(np.float64); a64 = a.reshape(-1).astype(np.float64)
+    worst = 0.0
+    for j in rows:
+        s, e = int(row_ptr[j]), int(row_ptr[j + 1])
+        w = tab64[code[s:e]]; xv = a64[col[s:e]]
+        y64 = 2.0 * float(c0[0, j]) + 1.3 * float(np.dot(w, xv))
+        bound = abs(2.0 * float(c0[0, j])) + 1.3 * float(np.dot(np.abs(w), np.abs(xv)))
+        worst = max(worst, abs(float(got[j]) - y64) / max(bound, 1e-300))
+    assert worst <= TOL, worst
+    again = dev.addmatmat_host(a, 1, k, c0.copy(), n, 1.3, 2.0).reshape(-1)
+    assert_bits_equal(again, got, "run-to-run determinism at full size")

@@ -393,6 +393,17 @@ def run_ours(args):
             line["cpu_baseline"] = {"value": flops / best / 1e9, "unit": "GFLOP/s", "cores": 1, "kind": ref.kind,
                                     "sample": ref.sample + f"; best of {reps}", "ms_per_step": best * 1e3,
                                     "host_cores_available": os.cpu_count()}
+            # the reference harness's own cross-check (blas_test.cc:16-19): dense sgemm on the CopyTo-expanded matrix,
+            # here numpy's bundled OpenBLAS on all host cores; reported in sparse flops per second, small configs only
+            if host_obj is not None and n * k <= (1 << 24):
+                w = np.where(inp["codes"] < 255, inp["tab"][np.minimum(inp["codes"], 254)], np.float32(0)).astype(np.float32)
+                a_h = inp["a"]
+                np.dot(a_h, w.T)
+                t_best = 1e9
+                for _ in range(3):
+                    t0 = time.perf_counter(); np.dot(a_h, w.T); t_best = min(t_best, time.perf_counter() - t0)
+                line["cpu_dense_openblas"] = {"value": flops / t_best / 1e9, "unit": "GFLOP/s (sparse flops)", "ms_per_step": t_best * 1e3,
+                                              "cores": os.cpu_count(), "what": "numpy.dot (bundled OpenBLAS, all cores) on the dense expansion"}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

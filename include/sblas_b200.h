@@ -44,6 +44,7 @@ extern "C" {
 #define SBLAS_B200_ECUDA    -2   /* a CUDA call failed, or no device */
 #define SBLAS_B200_ENOMEM   -3   /* host or device allocation failed */
 #define SBLAS_B200_EFORMAT  -4   /* the compressed stream / CSR is inconsistent */
+#define SBLAS_B200_EIO      -5   /* a file could not be opened, read or written */
 
 #define SBLAS_B200_ABI_VERSION 1
 

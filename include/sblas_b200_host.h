@@ -45,6 +45,17 @@ SBLAS_B200_API int32_t sblas_host_table_size(const sblas_host_matrix *h);  /* va
 SBLAS_B200_API void sblas_host_members(const sblas_host_matrix *h, const uint8_t **pos_index, const uint8_t **val_index,
                                        const float **val_table, const int32_t **block_bounds,
                                        const int32_t **block_index_bounds);
+/*
+ * Dump / load of the compressed members (the reference has no on-disk form), so that
+ * weights and test fixtures travel between boxes without repeating CopyForm.  Little-endian file:
+ *   "SBLASM1\0" | int32 rows, cols, valid_table_size, nblocks | int64 entries |
+ *   val_table[T+1] f32 | block_bounds[nblocks][2] i32 | block_index_bounds[nblocks][2] i32 |
+ *   pos_index[entries] u8 | val_index[entries] u8 | uint64 FNV-1a of everything before it.
+ * _load validates sizes, bounds, codes and the checksum before touching the object (SBLAS_B200_EFORMAT
+ * otherwise, SBLAS_B200_EIO when the file cannot be read), then replaces its contents like CopyForm does.
+ */
+SBLAS_B200_API int sblas_host_save(const sblas_host_matrix *h, const char *path);
+SBLAS_B200_API int sblas_host_load(sblas_host_matrix *h, const char *path);
 /* The device matrix of this object on the current CUDA device (uploads on first use); NULL on failure. */
 SBLAS_B200_API sblas_b200_matrix *sblas_host_device_matrix(sblas_host_matrix *h);
 

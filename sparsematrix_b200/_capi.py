@@ -10,7 +10,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("SBLAS_B200_LIB") or os.path.join(_HERE, "lib", "libsblas_b200.so")   # override: kernel experiments only
 
-OK, EINVAL, ECUDA, ENOMEM, EFORMAT = 0, -1, -2, -3, -4
+OK, EINVAL, ECUDA, ENOMEM, EFORMAT, EIO = 0, -1, -2, -3, -4, -5
 
 
 class SblasError(RuntimeError):
@@ -67,6 +67,8 @@ SYMBOLS = {
     "sblas_host_table_size": (_i32, [_vp]),
     "sblas_host_members": (None, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "sblas_host_device_matrix": (_vp, [_vp]),
+    "sblas_host_save": (C.c_int, [_vp, C.c_char_p]),
+    "sblas_host_load": (C.c_int, [_vp, C.c_char_p]),
 }
 
 _lib = None

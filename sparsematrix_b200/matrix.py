@@ -10,6 +10,7 @@ uploads (whole matrix, panel-aligned slab, direct CSR), the host- and device-poi
 products, and the structure read-backs used by the parity tests.
 """
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -241,6 +242,14 @@ class SparseMatrix:
 
         return (grab(p[0], n, np.uint8), grab(p[1], n, np.uint8), grab(p[2], T + 1 if T else 0, np.float32), T,
                 grab(p[3], 2 * nb, np.int32).reshape(-1, 2), grab(p[4], 2 * nb, np.int32).reshape(-1, 2))
+
+    def Save(self, path):
+        """sblas_host_save: the compressed members to a file (see include/sblas_b200_host.h)."""
+        _capi.check(self._L.sblas_host_save(self._h, os.fsencode(path)))
+
+    def Load(self, path):
+        """sblas_host_load: replace this object's contents with a saved matrix (validated first)."""
+        _capi.check(self._L.sblas_host_load(self._h, os.fsencode(path)))
 
     def device_matrix(self):
         """The uploaded matrix of this object on the current CUDA device (borrowed, owned by the object)."""

@@ -108,3 +108,42 @@ def test_argument_errors_are_reported_without_a_device():
     assert rc == _capi.EINVAL and b"valid_table_size" in L.sblas_b200_last_error()
     rc = L.sblas_b200_addmatmat_host(None, None, 1, 1, None, 1, 1.0, 1.0)
     assert rc == _capi.EINVAL
+
+
+def test_save_and_load_round_trip_and_reject_corruption(tmp_path):
+    """Dump / load of the compressed members (sblas_host_save / _load): equal object after a round trip,
+    nothing changes when the file is damaged, truncated or missing."""
+    from sparsematrix_b200 import gen
+    n, k = 300, 700
+    codes = gen.codes_bernoulli(n, k, 0.03, seed=71)
+    codes[:, 256:512] = 255                                    # an empty panel (Trans: S columns are the n rows; keep a gap in r instead)
+    tab = gen.codebook()
+    for trans in (sb.SparseMatrix.NoTrans, sb.SparseMatrix.Trans):
+        S = sb.SparseMatrix(codes, n, k, k, tab, 255, trans)
+        path = str(tmp_path / f"m{trans}.sblas")
+        S.Save(path)
+        L = sb.SparseMatrix()
+        L.Load(path)
+        assert L == S and L.NumRows() == S.NumRows() and L.NumCols() == S.NumCols()
+        for x, y in zip(L.members(), S.members()):
+            assert np.array_equal(np.asarray(x), np.asarray(y))
+        raw = bytearray(open(path, "rb").read())
+        keep = sb.SparseMatrix(codes[:10], 10, k, k, tab, 255, trans)
+        before = keep.members()
+        for name, data in (("flipped", bytes(raw[:100]) + bytes([raw[100] ^ 0x40]) + bytes(raw[101:])),
+                           ("truncated", bytes(raw[:-9])), ("trailing", bytes(raw) + b"x"), ("magic", b"NOTSBLAS" + bytes(raw[8:]))):
+            bad = str(tmp_path / f"{name}.sblas")
+            open(bad, "wb").write(data)
+            with pytest.raises(sb.SblasError) as ei:
+                keep.Load(bad)
+            assert ei.value.code == _capi.EFORMAT, name
+            for x, y in zip(keep.members(), before):
+                assert np.array_equal(np.asarray(x), np.asarray(y)), name
+        with pytest.raises(sb.SblasError) as ei:
+            keep.Load(str(tmp_path / "missing.sblas"))
+        assert ei.value.code == _capi.EIO
+    E = sb.SparseMatrix()                                      # empty object
+    E.Save(str(tmp_path / "empty.sblas"))
+    F = sb.SparseMatrix(codes, n, k, k, tab, 255, 0)
+    F.Load(str(tmp_path / "empty.sblas"))
+    assert F == E and F.NumRows() == 0 and F.NumCols() == 0

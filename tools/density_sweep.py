@@ -52,8 +52,8 @@ def main():
     dev = torch.device("cuda", 0)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     tab = gen.codebook(255, 1)
-    print("| n=k | sparsity | m | nnz | GPU cold us | GPU warm us | GPU GFLOP/s (cold) | ref CPU ms (1 thread) | CPU GFLOP/s | GPU/CPU |")
-    print("|---|---|---|---|---|---|---|---|---|---|")
+    print("| n=k | sparsity | m | nnz | GPU cold us | GPU warm us | GPU GFLOP/s (cold) | ref CPU ms (1 thread) | CPU GFLOP/s | GPU/CPU | dense OpenBLAS ms (numpy.dot, all cores) |")
+    print("|---|---|---|---|---|---|---|---|---|---|---|")
     sizes = args.sizes or ([4096] + ([16384] if args.big else []))
     for n in sizes:
         for idx, sp in enumerate([50.0, 75.0, 90.0, 95.0, 99.0, 99.9]):
@@ -82,7 +82,12 @@ def main():
                         R.AddMatMat(a, m, n, c, n, 1.0, 1.0)
                         best = min(best, time.perf_counter() - t0)
                     cpu_ms, cpu_gf, ratio = best * 1e3, flops / best / 1e9, best * 1e6 / cold
-                print(f"| {n} | {sp}% | {m} | {nnz} | {cold:.1f} | {warm:.1f} | {flops / cold / 1e3:.1f} | {cpu_ms:.2f} | {cpu_gf:.2f} | {ratio:.0f}x |", flush=True)
+                dense_ms = float("nan")
+                if R is not None:                             # the reference harness's cross-check: sgemm on the dense expansion
+                    w = np.where(codes < 255, tab[np.minimum(codes, 254)], np.float32(0)).astype(np.float32)
+                    np.dot(a, w.T)
+                    t0 = time.perf_counter(); np.dot(a, w.T); dense_ms = (time.perf_counter() - t0) * 1e3
+                print(f"| {n} | {sp}% | {m} | {nnz} | {cold:.1f} | {warm:.1f} | {flops / cold / 1e3:.1f} | {cpu_ms:.2f} | {cpu_gf:.2f} | {ratio:.0f}x | {dense_ms:.2f} |", flush=True)
             del S, mat
 
 

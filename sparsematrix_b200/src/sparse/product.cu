@@ -410,8 +410,17 @@ int product_on_stream(sblas_b200_matrix *mat, const float *d_a, int32_t m, int32
         }
         return SBLAS_B200_OK;
     }
-    if (m == 1) return run_spmv(mat, d_a, d_c, alpha, beta, stream);
-    return run_spmm(mat, d_a, m, lda, d_c, ldc, alpha, beta, stream);
+    // Xt staging and split-row partials belong to the handle: order this product after the previous one
+    // when that ran on a different stream
+    if (!mat->ws_event) SB_CUDA(cudaEventCreateWithFlags(&mat->ws_event, cudaEventDisableTiming));
+    if (mat->ws_used && mat->ws_stream != stream) SB_CUDA(cudaStreamWaitEvent(stream, mat->ws_event, 0));
+    const int rc = m == 1 ? run_spmv(mat, d_a, d_c, alpha, beta, stream) : run_spmm(mat, d_a, m, lda, d_c, ldc, alpha, beta, stream);
+    if (rc == SBLAS_B200_OK) {
+        SB_CUDA(cudaEventRecord(mat->ws_event, stream));
+        mat->ws_stream = stream;
+        mat->ws_used = true;
+    }
+    return rc;
 }
 
 static int check_product_args(const sblas_b200_matrix *mat, const float *a, int32_t m, int32_t lda, const float *c,

@@ -431,6 +431,7 @@ static void release(sblas_b200_matrix *mat) {
     cudaFree(mat->d_ws); cudaFree(mat->d_partial); cudaFree(mat->d_host_a); cudaFree(mat->d_host_c);
     cudaFree(mat->d_host_p);
     if (mat->stream) cudaStreamDestroy(mat->stream);
+    if (mat->ws_event) cudaEventDestroy(mat->ws_event);
     if (mat->stream2) cudaStreamDestroy(mat->stream2);
     if (mat->stream3) cudaStreamDestroy(mat->stream3);
     for (cudaEvent_t ev : mat->host_events) cudaEventDestroy(ev);

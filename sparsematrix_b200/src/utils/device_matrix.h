@@ -114,6 +114,11 @@ struct sblas_b200_matrix {
     float *d_host_a = nullptr;  size_t host_a_bytes = 0;   // host path: A on device
     float *d_host_c = nullptr;  size_t host_c_bytes = 0;   // host path: C on device
     cudaStream_t stream = nullptr;                          // host path stream
+    // the workspace is shared by every product of the handle: a product enqueued on another stream than the
+    // previous one first waits for that one's event (same stream: stream order is enough)
+    cudaEvent_t ws_event = nullptr;
+    cudaStream_t ws_stream = nullptr;
+    bool ws_used = false;
     // host path, pinned caller buffers: the product runs into d_host_p (kept at -0.0f between calls)
     // while C travels in on stream2; one kernel then combines both straight into the caller's C
     float *d_host_p = nullptr;  size_t host_p_bytes = 0;   bool host_p_clean = false;

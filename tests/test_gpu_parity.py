@@ -604,3 +604,25 @@ def test_config4_full_size_sampled_rows():
     assert worst <= TOL, worst
     again = dev.addmatmat_host(a, 1, k, c0.copy(), n, 1.3, 2.0).reshape(-1)
     assert_bits_equal(again, got, "run-to-run determinism at full size")
+
+
+def test_products_of_one_handle_on_two_streams_are_ordered_by_the_library():
+    """The Xt staging buffer belongs to the handle; products enqueued on different streams must be
+    ordered by the library (event), not race on it."""
+    import torch
+    n, k, m = 2048, 2048, 96
+    codes = gen.codes_bernoulli(n, k, 0.05, seed=81)
+    tab = gen.codebook()
+    dev = upload(O.copyform(codes, n, k, k, tab, 255, True))
+    a1 = torch.from_numpy(gen.dense_uniform((m, k), 1)).cuda(); a2 = torch.from_numpy(gen.dense_uniform((m, k), 2)).cuda()
+    want1 = torch.zeros((m, n), device="cuda"); want2 = torch.zeros((m, n), device="cuda")
+    dev.addmatmat_dev(a1, m, k, want1, n, 1.0, 0.0); dev.addmatmat_dev(a2, m, k, want2, n, 1.0, 0.0)
+    torch.cuda.synchronize()
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    for _ in range(20):
+        c1 = torch.zeros((m, n), device="cuda"); c2 = torch.zeros((m, n), device="cuda")
+        torch.cuda.synchronize()
+        dev.addmatmat_dev(a1, m, k, c1, n, 1.0, 0.0, stream=s1.cuda_stream)
+        dev.addmatmat_dev(a2, m, k, c2, n, 1.0, 0.0, stream=s2.cuda_stream)
+        torch.cuda.synchronize()
+        assert torch.equal(c1, want1) and torch.equal(c2, want2)

@@ -168,7 +168,11 @@ SBLAS_B200_API int sblas_b200_addmatmat_host(sblas_b200_matrix *mat, const float
 /*
  * The same product on DEVICE pointers (on mat's device), enqueued on `stream`
  * (a cudaStream_t; NULL = the default stream) and not synchronised.  This is
- * the timed path.
+ * the timed path.  Calls on one handle may come from several threads and
+ * streams: the handle's workspace is shared, so a product enqueued on another
+ * stream than the previous one is ordered after it with an event (products on
+ * different handles run concurrently).  With pinned host buffers
+ * sblas_b200_addmatmat_host() overlaps its copies with the product.
  */
 SBLAS_B200_API int sblas_b200_addmatmat_dev(sblas_b200_matrix *mat, const float *d_a, int32_t m, int32_t lda,
                                             float *d_c, int32_t ldc, float alpha, float beta, void *stream);

@@ -376,7 +376,10 @@ static void launch_spmm_gather(const sblas_b200_matrix *mat, const float *xt, in
 static int run_spmm(sblas_b200_matrix *mat, const float *d_a, int m, int lda, float *d_c, int ldc, float alpha,
                     float beta, cudaStream_t stream) {
     // large m: X staged through shared memory (src/sparse/spmm_tile.cu) once the tile format exists
-    int tile_min_m = 17;
+    // Small m too, unless the (row, chunk) pieces are nearly empty: measured (profiles/r01c_small_m.md) the tile
+    // kernel beats the gather kernel 2-3x at m = 2..16 from ~3 entries per piece, and loses 30 % below that.
+    const double per_piece = (double)mat->nnz / ((double)std::max(1, mat->n) * ((mat->k + kTileK - 1) / kTileK));
+    int tile_min_m = per_piece >= 3.0 ? 2 : 17;
     if (const char *env = getenv("SBLAS_B200_TILE_MIN_M")) tile_min_m = atoi(env);
     if (m >= tile_min_m) {
         const int trc = run_spmm_tile(mat, d_a, m, lda, d_c, ldc, alpha, beta, stream);

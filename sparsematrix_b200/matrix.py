@@ -206,6 +206,9 @@ class SparseMatrix:
     def CopyTo(self, stride, trans=0):
         """Returns the dense matrix (NumRows x stride, or NumCols x stride when trans)."""
         lead = self.NumCols() if trans else self.NumRows()
+        minor = self.NumRows() if trans else self.NumCols()
+        if stride < minor:
+            raise ValueError(f"stride {stride} < {minor}: the dense output would be overrun")
         dense = np.full((lead, stride), np.float32(1.0), np.float32)
         self._L.sblas_host_copyto(self._h, _ptr(dense), stride, int(trans))
         return dense

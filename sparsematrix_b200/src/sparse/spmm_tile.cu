@@ -158,18 +158,19 @@ transpose_in_tiled_kernel(const float *__restrict__ a, int m, int k, int lda, fl
 
 
 // blockDim.x = (nwarps + 1) * 32: nwarps consumer warps and one producer warp (the last).
-// RS = W rows per slot (a warp owns 4*RS rows).  HALF (with NF4 = 1, for m <= 16): the m-tile is 16 columns
-// wide; the two halves of a slot (4 lanes each) take the even and the odd entries of the slot's
-// row at the same time and their sums are added at the end -- half the shared-memory wavefronts
-// per entry, at the price of a summation order that is no longer strictly column by column.
-template <int RS, int NF4, int STAGES, bool SCALE, int HALF>
+// RS = W rows per slot (a warp owns 4*RS rows).  SPLIT = 2 | 4 (with NF4 = 1, for m <= 16 | 8): the m-tile is
+// 16 | 8 columns wide; the 8 lanes of a slot form SPLIT parts that take SPLIT consecutive entries
+// of the slot's row at the same time, and their sums are added at the end -- 1/SPLIT of the
+// shared-memory wavefronts per entry, at the price of a summation order that is no longer strictly
+// column by column.
+template <int RS, int NF4, int STAGES, bool SCALE, int SPLIT>
 __global__ void __maxnreg__((RS == 1 && NF4 == 1) ? 64 : TILE_MAXNREG_BIG)
 spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__ grp_ptr,
                  const uint32_t *__restrict__ grp_nq, const int32_t *__restrict__ row_ptr, int ngroups, int nchunks,
                  int n, const float *__restrict__ xt, int k_alloc, float *__restrict__ c, int ldc, int m, float alpha,
                  float beta, int nwarps) {
-    constexpr int MT = HALF ? 16 : 32 * NF4, G = 4 * RS;
-    static_assert(!HALF || NF4 == 1, "the half-width tile has one float4 per lane");
+    constexpr int MT = 32 * NF4 / SPLIT, G = 4 * RS;
+    static_assert(SPLIT == 1 || ((SPLIT == 2 || SPLIT == 4) && NF4 == 1), "narrow tiles have one float4 per lane");
     constexpr int STAGE_BYTES = 256 * MT * 4;                    // 255 data rows, padded to a round size
     constexpr uint32_t CHUNK_BYTES = kTileK * MT * 4;
     extern __shared__ __align__(128) uint8_t smem_raw[];
@@ -180,7 +181,7 @@ spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__
     __shared__ int s_len[kMaxRows];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int slot = lane >> 3, c8 = HALF ? (lane & 3) : (lane & 7), half = HALF ? ((lane >> 2) & 1) : 0;
+    const int slot = lane >> 3, c8 = lane & (8 / SPLIT - 1), part = (lane & 7) / (8 / SPLIT);   // column lane, part of the slot
     const int RB = nwarps * G;
     // 1-D grid, m-tile fastest: the CTAs that share a block of W rows are neighbours in launch order,
     // so the quad rows are read from HBM once and served from L2 to the other m-tiles
@@ -287,9 +288,12 @@ spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__
                 cur_r = *reinterpret_cast<const uint32_t *>(rp + roff);
                 rp += kBlockBytes;
                 if (SCALE) { w.x *= alpha; w.y *= alpha; w.z *= alpha; w.w *= alpha; }
-                if (HALF) {                                      // entries 0|1, then 2|3, one per half of the slot
-                    slot_step<NF4, MT * 4>(a, xr[0], half ? w.y : w.x, __byte_perm(r4, 0u, 0x4440u + half), xbase);
-                    slot_step<NF4, MT * 4>(a, xr[1], half ? w.w : w.z, __byte_perm(r4, 0u, 0x4442u + half), xbase);
+                if (SPLIT == 4) {                                // entries 0..3, one per quarter of the slot
+                    const float wp = part < 2 ? (part ? w.y : w.x) : (part == 2 ? w.z : w.w);
+                    slot_step<NF4, MT * 4>(a, xr[0], wp, __byte_perm(r4, 0u, 0x4440u + part), xbase);
+                } else if (SPLIT == 2) {                         // entries 0|1, then 2|3, one per half of the slot
+                    slot_step<NF4, MT * 4>(a, xr[0], part ? w.y : w.x, __byte_perm(r4, 0u, 0x4440u + part), xbase);
+                    slot_step<NF4, MT * 4>(a, xr[1], part ? w.w : w.z, __byte_perm(r4, 0u, 0x4442u + part), xbase);
                 } else {
                     slot_step<NF4, MT * 4>(a, xr[0], w.x, __byte_perm(r4, 0u, 0x4440u), xbase);
                     slot_step<NF4, MT * 4>(a, xr[1], w.y, __byte_perm(r4, 0u, 0x4441u), xbase);
@@ -329,12 +333,15 @@ spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__
         for (int rr = 0; rr < RS; ++rr)
 #pragma unroll
             for (int f = 0; f < NF4; ++f) {
-                if (HALF) {                                      // even-entry sums + odd-entry sums
-                    acc[rr][f].x += __shfl_xor_sync(0xffffffffu, acc[rr][f].x, 4);
-                    acc[rr][f].y += __shfl_xor_sync(0xffffffffu, acc[rr][f].y, 4);
-                    acc[rr][f].z += __shfl_xor_sync(0xffffffffu, acc[rr][f].z, 4);
-                    acc[rr][f].w += __shfl_xor_sync(0xffffffffu, acc[rr][f].w, 4);
-                    if (half) continue;
+                if (SPLIT > 1) {                                 // add the parts' sums (fixed order)
+#pragma unroll
+                    for (int o = 8 / SPLIT; o < 8; o <<= 1) {
+                        acc[rr][f].x += __shfl_xor_sync(0xffffffffu, acc[rr][f].x, o);
+                        acc[rr][f].y += __shfl_xor_sync(0xffffffffu, acc[rr][f].y, o);
+                        acc[rr][f].z += __shfl_xor_sync(0xffffffffu, acc[rr][f].z, o);
+                        acc[rr][f].w += __shfl_xor_sync(0xffffffffu, acc[rr][f].w, o);
+                    }
+                    if (part) continue;
                 }
                 float *p = tile + (size_t)(warp * G + rr * 4 + slot) * (MT + 1) + 32 * f + c8 * 4;
                 p[0] = acc[rr][f].x; p[1] = acc[rr][f].y; p[2] = acc[rr][f].z; p[3] = acc[rr][f].w;
@@ -388,10 +395,10 @@ static void dump_timeline() {
 }
 #endif
 
-template <int RS, int NF4, int STAGES, int HALF = 0>
+template <int RS, int NF4, int STAGES, int SPLIT = 1>
 static int launch_tile(const sblas_b200_matrix *mat, const TileFormat &tf, const float *xt, int k_alloc, float *d_c,
                        int ldc, int m, float alpha, float beta, int nwarps, cudaStream_t stream) {
-    constexpr int MT = HALF ? 16 : 32 * NF4, MAXW = kMaxRows / (4 * RS);
+    constexpr int MT = 32 * NF4 / SPLIT, MAXW = kMaxRows / (4 * RS);
     const int nchunks = tf.nchunks;
     auto smem_for = [nchunks](int nw) { return (size_t)STAGES * 256 * MT * 4 + (size_t)nw * kRingBytes + 2 * STAGES * 8 + (size_t)nw * nchunks * 4; };
     if (smem_for(nwarps) > 226 * 1024) return 1;                  // k too long for the per-chunk counts: gather kernel
@@ -399,8 +406,8 @@ static int launch_tile(const sblas_b200_matrix *mat, const TileFormat &tf, const
     bool &configured = configured_on[mat->device & 63];
     if (!configured) {
         (void)MAXW;
-        SB_CUDA(cudaFuncSetAttribute(spmm_tile_kernel<RS, NF4, STAGES, false, HALF>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
-        SB_CUDA(cudaFuncSetAttribute(spmm_tile_kernel<RS, NF4, STAGES, true, HALF>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+        SB_CUDA(cudaFuncSetAttribute(spmm_tile_kernel<RS, NF4, STAGES, false, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+        SB_CUDA(cudaFuncSetAttribute(spmm_tile_kernel<RS, NF4, STAGES, true, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
         configured = true;
     }
     const dim3 grid(((tf.ngroups + nwarps - 1) / nwarps) * ((m + MT - 1) / MT));
@@ -420,7 +427,7 @@ static int launch_tile(const sblas_b200_matrix *mat, const TileFormat &tf, const
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     const int ngroups = tf.ngroups, n = mat->n;
-    auto kernel = alpha == 1.0f ? spmm_tile_kernel<RS, NF4, STAGES, false, HALF> : spmm_tile_kernel<RS, NF4, STAGES, true, HALF>;
+    auto kernel = alpha == 1.0f ? spmm_tile_kernel<RS, NF4, STAGES, false, SPLIT> : spmm_tile_kernel<RS, NF4, STAGES, true, SPLIT>;
     SB_CUDA(cudaLaunchKernelEx(&cfg, kernel, (const uint8_t *)tf.d_blocks, (const int32_t *)tf.d_grp_ptr,
                                (const uint32_t *)tf.d_grp_nq, (const int32_t *)mat->d_row_ptr, ngroups, nchunks, n, xt,
                                k_alloc, d_c, ldc, m, alpha, beta, nwarps));
@@ -430,7 +437,7 @@ static int launch_tile(const sblas_b200_matrix *mat, const TileFormat &tf, const
 }
 
 namespace {
-struct TilePlan { int rs, nf4, nwarps, half; };
+struct TilePlan { int rs, nf4, nwarps, split; };
 
 // Pick rows per slot, float4s per lane and consumer warps per CTA.  One CTA per SM at a time, so a
 // launch costs (waves of CTAs) x (time of one CTA); the time of one CTA is a fixed part (cold start,
@@ -441,22 +448,25 @@ TilePlan plan_tile(const sblas_b200_matrix *mat, int m, int sms) {
     const double fixed = 8000.0, eff = 0.75;
     const int nchunks = (mat->k + kTileK - 1) / kTileK;
     const double quads = 1.25 * (double)mat->nnz / std::max(1, mat->n) / 4.0 + 0.5 * nchunks;   // per 4-row set
-    const int half = m <= 16 ? 1 : 0;                            // 16-column tile, two entries of a slot per step
-    TilePlan best = {2, 1, 16, half};
+    // 8- / 16-column tile, 4 / 2 entries of a slot per step; the 8-column tile pays only on large matrices
+    // (16384^2 at 90 %: 120 -> 95 us; 4096^2 at 90 %: 26 -> 32 us, profiles/r01c_small_m.md)
+    const int split = (m <= 8 && mat->nnz >= (6 << 20)) ? 4 : (m <= 16 ? 2 : 1);
+    TilePlan best = {2, 1, 16, split};
     double best_cost = 1e300;
     for (int rs = 1; rs <= 2; ++rs)
         for (int nf4 = 1; nf4 <= 2; ++nf4) {
             if (nf4 == 2 && m <= 32) continue;
             const int max_w = (rs == 1 && nf4 == 1) ? 28 : TILE_MAXW_BIG;
-            const double instr = half ? 24.0 : (nf4 == 1 ? 38.0 : 55.0), lat = half ? 60.0 : (nf4 == 1 ? 90.0 : 110.0);
-            const int mtiles = half ? 1 : (m + 32 * nf4 - 1) / (32 * nf4);
+            const double instr = split == 4 ? 16.0 : (split == 2 ? 24.0 : (nf4 == 1 ? 38.0 : 55.0));
+            const double lat = split > 1 ? 60.0 : (nf4 == 1 ? 90.0 : 110.0);
+            const int mtiles = split > 1 ? 1 : (m + 32 * nf4 - 1) / (32 * nf4);
             const int ngroups = (mat->n + 4 * rs - 1) / (4 * rs);
             for (int nw = 4; nw <= max_w; ++nw) {
                 const int64_t ctas = (int64_t)((ngroups + nw - 1) / nw) * mtiles;
                 const int64_t waves = (ctas + sms - 1) / sms;
                 const double per_quad = std::max(instr * ((nw + 3) / 4) / eff, lat);
                 const double cost = (double)waves * (fixed + rs * quads * per_quad);
-                if (cost < best_cost * (1.0 - 1e-9)) { best_cost = cost; best = {rs, nf4, nw, half}; }
+                if (cost < best_cost * (1.0 - 1e-9)) { best_cost = cost; best = {rs, nf4, nw, split}; }
             }
         }
     return best;
@@ -474,7 +484,7 @@ int run_spmm_tile(sblas_b200_matrix *mat, const float *d_a, int m, int lda, floa
     if (const char *env = getenv("SBLAS_B200_TILE")) {
         if ((env[0] == '1' || env[0] == '2') && (env[1] == '1' || env[1] == '2') && env[2] && env[3]) {
             plan.rs = env[0] - '0';
-            plan.nf4 = plan.half ? 1 : env[1] - '0';
+            plan.nf4 = plan.split > 1 ? 1 : env[1] - '0';
             plan.nwarps = std::min((plan.rs == 1 && plan.nf4 == 1) ? 28 : TILE_MAXW_BIG, std::max(1, atoi(env + 2)));
         }
     }
@@ -484,7 +494,7 @@ int run_spmm_tile(sblas_b200_matrix *mat, const float *d_a, int m, int lda, floa
         if (brc != SBLAS_B200_OK) return brc;
     }
     if (tf.state != 1) return 1;                                  // no tile layout for this matrix: caller falls back to the gather kernel
-    const int MT = plan.half ? 16 : 32 * plan.nf4;
+    const int MT = 32 * plan.nf4 / plan.split;
     const int ntiles = (m + MT - 1) / MT;
     const int k_alloc = tf.nchunks * kTileK;
     int rc = ensure_buffer(&mat->d_ws, &mat->ws_bytes, (size_t)ntiles * k_alloc * MT * 4);
@@ -500,8 +510,10 @@ int run_spmm_tile(sblas_b200_matrix *mat, const float *d_a, int m, int lda, floa
         ~Timer() { if (a) { cudaEventRecord(b, st); mat->prof_events.push_back(std::make_pair(a, b)); } }
     } timer(mat, stream);
     const float *xt = mat->d_ws;
-    if (plan.half && plan.rs == 1) return launch_tile<1, 1, 4, 1>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, stream);
-    if (plan.half) return launch_tile<2, 1, 4, 1>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, stream);
+    if (plan.split == 4 && plan.rs == 1) return launch_tile<1, 1, 4, 4>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, stream);
+    if (plan.split == 4) return launch_tile<2, 1, 4, 4>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, stream);
+    if (plan.split == 2 && plan.rs == 1) return launch_tile<1, 1, 4, 2>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, stream);
+    if (plan.split == 2) return launch_tile<2, 1, 4, 2>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, stream);
     if (plan.rs == 1 && plan.nf4 == 1) return launch_tile<1, 1, 3>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, stream);
     if (plan.rs == 1) return launch_tile<1, 2, 2>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, stream);
     if (plan.nf4 == 1) return launch_tile<2, 1, 3>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, stream);

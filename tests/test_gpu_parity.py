@@ -407,7 +407,7 @@ def test_device_copyform_edge_cases_and_host_class_route():
     for x, y in zip(H.members(), D.members()):
         assert np.array_equal(np.asarray(x), np.asarray(y))
     assert_bits_equal(D.AddMatMat(a, 5, k, c0.copy(), n, 1.3, 2.0), H.AddMatMat(a, 5, k, c0.copy(), n, 1.3, 2.0), "device-built vs host-built object")
-    assert np.array_equal(D.CopyTo(n, sb.SparseMatrix.Trans), H.CopyTo(n, sb.SparseMatrix.Trans))
+    assert np.array_equal(D.CopyTo(k, sb.SparseMatrix.Trans), H.CopyTo(k, sb.SparseMatrix.Trans))    # S^T is n x k: stride >= k
 
 
 def test_decode_dense_into_device_memory():
@@ -626,3 +626,27 @@ def test_products_of_one_handle_on_two_streams_are_ordered_by_the_library():
         dev.addmatmat_dev(a2, m, k, c2, n, 1.0, 0.0, stream=s2.cuda_stream)
         torch.cuda.synchronize()
         assert torch.equal(c1, want1) and torch.equal(c2, want2)
+
+
+def test_narrow_tiles_for_small_m_on_a_large_matrix():
+    """m <= 16 takes the 16-column tile (two entries of a slot per step), m <= 8 on a matrix of >= 6 Mi
+    non-zeros the 8-column tile (four per step): sampled rows against fp64, and one output element
+    does not depend on which other A rows are in the call within the same tile width."""
+    n = k = 8192
+    codes = gen.codes_bernoulli(n, k, 0.10, seed=91)           # 6.7 M non-zeros
+    tab = gen.codebook()
+    S = sb.SparseMatrix(codes, n, k, k, tab, 255, 1)
+    dev = S.device_matrix()
+    assert dev.nnz >= (6 << 20)
+    rows = np.random.default_rng(7).choice(n, 40, replace=False)
+    for m in (2, 5, 8, 9, 16):
+        a = gen.dense_uniform((m, k), 90 + m); c0 = gen.dense_uniform((m, n + 4), 91 + m)
+        got = dev.addmatmat_host(a, m, k, c0.copy(), n + 4, 1.3, 2.0)
+        err = _sampled_backward_error(got[:, rows], codes[rows], tab, a, c0[:, rows], 1.3, 2.0)
+        assert err <= TOL, (m, err)
+        again = dev.addmatmat_host(a, m, k, c0.copy(), n + 4, 1.3, 2.0)
+        assert_bits_equal(again, got, f"determinism m={m}")
+    a = gen.dense_uniform((8, k), 3); c0 = gen.dense_uniform((8, n), 4)
+    full = dev.addmatmat_host(a, 8, k, c0.copy(), n, 1.0, 1.0)
+    part = dev.addmatmat_host(a[2:5], 3, k, c0[2:5].copy(), n, 1.0, 1.0)
+    assert_bits_equal(part, full[2:5], "m = 3 vs rows 2..4 of m = 8 (same 8-column tile)")

@@ -30,6 +30,17 @@ def _ptr(x):
     raise TypeError(type(x))
 
 
+def _need(x, count, what):
+    """Refuse buffers shorter than the library will touch (numpy arrays / torch tensors; raw ints are trusted)."""
+    have = None
+    if isinstance(x, np.ndarray):
+        have = x.size
+    elif hasattr(x, "numel"):
+        have = x.numel()
+    if have is not None and have < count:
+        raise ValueError(f"{what} holds {have} elements, the call needs {count}")
+
+
 def _f32c(a):
     a = np.asarray(a)
     if a.dtype != np.float32 or not a.flags.c_contiguous:
@@ -104,14 +115,28 @@ class DeviceMatrix:
     def nnz(self):
         return self.info().nnz
 
+    def _shape(self):
+        """(n, k), fetched once: a handle never changes shape."""
+        sh = getattr(self, "_nk", None)
+        if sh is None:
+            inf = self.info()
+            sh = self._nk = (inf.s_cols, inf.s_rows)
+        return sh
+
     # ---- the product ----------------------------------------------------------------------
     def addmatmat_host(self, a, m, lda, c, ldc, alpha, beta):
         """C = beta*C + alpha*A*S on host buffers (numpy or pinned torch tensors), in place on c."""
+        if m > 0:
+            n, k = self._shape()
+            _need(a, (m - 1) * lda + k, "a"); _need(c, (m - 1) * ldc + n, "c")
         _capi.check(_capi.lib().sblas_b200_addmatmat_host(self._h, _ptr(a), m, lda, _ptr(c), ldc, alpha, beta))
         return c
 
     def addmatmat_dev(self, d_a, m, lda, d_c, ldc, alpha, beta, stream=0):
         """Same on device pointers (torch CUDA tensors or raw ints), enqueued on `stream` (cudaStream_t as int)."""
+        if m > 0:
+            n, k = self._shape()
+            _need(d_a, (m - 1) * lda + k, "d_a"); _need(d_c, (m - 1) * ldc + n, "d_c")
         _capi.check(_capi.lib().sblas_b200_addmatmat_dev(self._h, _ptr(d_a), m, lda, _ptr(d_c), ldc, alpha, beta,
                                                          C.c_void_p(stream) if stream else None))
 
@@ -215,6 +240,8 @@ class SparseMatrix:
 
     def AddMatMat(self, a, m, lda, c, ldc, alpha, beta):
         """In place on c; a and c are host buffers (numpy float32 / pinned torch tensors)."""
+        if m > 0:
+            _need(a, (m - 1) * lda + self.NumRows(), "a"); _need(c, (m - 1) * ldc + self.NumCols(), "c")
         _capi.check(self._L.sblas_host_addmatmat(self._h, _ptr(a), m, lda, _ptr(c), ldc, alpha, beta))
         return c
 

@@ -314,7 +314,7 @@ def run_ours(args):
     checksum = float(h_c.sum())
 
     # optional reassembly of Y on every rank (not part of `value`: the path itself has no collective)
-    gather_ms = None
+    gather_ms = peer_ms = None
     if world > 1:
         from sparsematrix_b200 import sharding
         splits = [r * n for r in range(world + 1)]
@@ -328,11 +328,37 @@ def run_ours(args):
         g1.record(stream)
         barrier()
         gather_ms = g0.elapsed_time(g1) / 5
+        # the same reassembly without a collective: every rank's kernels store their slab of C straight into
+        # rank 0's memory through an NVLink-mapped pointer (sharding.PeerOutput); product + "gather" in one launch
+        try:
+            out = sharding.PeerOutput(m, world * n, root=0, device=local_rank)
+            if rank == 0:
+                out.tensor().zero_()
+            out.finish()
+            for _ in range(3):
+                out.write_slab(mat, d_a, k, rank * n, 1.0, 1.0, stream=stream.cuda_stream)
+            out.finish()
+            p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            p0.record(stream)
+            for _ in range(10):
+                out.write_slab(mat, d_a, k, rank * n, 1.0, 1.0, stream=stream.cuda_stream)
+            p1.record(stream)
+            out.finish()
+            peer_ms = p0.elapsed_time(p1) / 10
+            out.close()
+        except Exception as e:                                  # auxiliary figure: never lose the bench line over it
+            peer_ms = None
+            print(f"bench.py: peer-mapped output unavailable on rank {rank}: {e}", file=sys.stderr)
 
     t = torch.tensor([total_ms, warm_ms, e2e_s * 1e3, kern_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     total_ms, warm_ms, e2e_ms, kern_ms_max = [float(x) for x in t.tolist()]
+    peer_ms_max = None
+    if world > 1:
+        pt = torch.tensor([peer_ms if peer_ms is not None else float("inf")], dtype=torch.float64, device=dev)
+        dist.all_reduce(pt, op=dist.ReduceOp.MAX)
+        peer_ms_max = float(pt.item()) if pt.item() != float("inf") else None
 
     if rank == 0:
         hbm_peak, peak_src = measured_peaks()
@@ -385,6 +411,8 @@ def run_ours(args):
                 line["roofline"]["traffic_source"] = tr["source"]
         if gather_ms is not None:
             line["reassembly_allgather_ms"] = gather_ms
+        if peer_ms_max is not None:
+            line["reassembly_peer_store"] = {"ms_per_step": peer_ms_max, "what": "product with C on rank 0's GPU, every rank storing its slab over NVLink (warm L2, 10 steps, max over ranks); compare with ms_per_step (local C) + reassembly_allgather_ms"}
         if args.cpu_baseline and world >= 1:
             ref = CpuReference(inp)
             ref.call()

@@ -177,6 +177,29 @@ SBLAS_B200_API int sblas_b200_addmatmat_host(sblas_b200_matrix *mat, const float
 SBLAS_B200_API int sblas_b200_addmatmat_dev(sblas_b200_matrix *mat, const float *d_a, int32_t m, int32_t lda,
                                             float *d_c, int32_t ldc, float alpha, float beta, void *stream);
 
+/* ---- peer-visible output: reassembly across GPUs without a collective ------ */
+/*
+ * The slabs of sblas_b200_upload_slab() write disjoint column ranges of C (the
+ * reference's panel loop, sparse-matrix.cc:164-190, has the same independence),
+ * so the whole C can be assembled on one GPU by letting every rank's product
+ * kernels store through an NVLink-mapped pointer: d_c = base + col_begin,
+ * ldc = n in sblas_b200_addmatmat_dev().  One process per GPU, so the mapping
+ * goes through a CUDA IPC handle (64 opaque bytes, sent by any channel):
+ *   _peer_alloc : cudaMalloc on `device` + the handle of that allocation
+ *   _peer_open  : map another process's allocation into this process for `device`
+ *                 (peer access is enabled on first use); not for the owner itself
+ *   _peer_close : unmap a pointer of _peer_open
+ *   _peer_free  : free a pointer of _peer_alloc (after every peer has closed it)
+ * The owner must not read C before the writers' streams have been synchronised
+ * (an application-level barrier); stores to peer memory are not ordered with
+ * the owner's own stream.
+ */
+#define SBLAS_B200_IPC_HANDLE_BYTES 64
+SBLAS_B200_API int sblas_b200_peer_alloc(int32_t device, int64_t bytes, void **d_ptr, uint8_t *handle);
+SBLAS_B200_API int sblas_b200_peer_open(int32_t device, const uint8_t *handle, void **d_ptr);
+SBLAS_B200_API int sblas_b200_peer_close(void *d_ptr);
+SBLAS_B200_API int sblas_b200_peer_free(void *d_ptr);
+
 /* ---- kernel timing (bench.py's roofline leg) ------------------------------ */
 /*
  * Between _begin and _end every product on this handle brackets its dominant

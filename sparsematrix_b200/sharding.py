@@ -5,6 +5,9 @@ reference already treats independently, sparse-matrix.cc:164-190) are split into
 panel-aligned, nnz-balanced slabs (``sblas_b200_partition``); slab g lives on GPU g, X is
 replicated, every GPU writes its own Y slab.  A collective is needed only when the output must
 be reassembled on every rank: ``gather_output`` is an all-gather of the (padded) C slabs.
+When the whole C is wanted on ONE GPU there is a way without any collective: ``PeerOutput``
+holds C on the root GPU and maps it into every rank over NVLink (CUDA IPC), and each rank's
+product kernels store their slab through that pointer -- product and "gather" are one launch.
 
 One process per GPU; ``torch.distributed`` (NCCL on GPUs, gloo on CPU for the tests) is the
 plumbing.  Nothing here computes: the product is ``DeviceMatrix.addmatmat_dev`` on the local slab.
@@ -54,6 +57,97 @@ def gather_output(c_local, m: int, splits, group=None):
         if widths[g]:
             out[:, int(splits[g]): int(splits[g + 1])] = recv[g, : widths[g]].t()
     return out
+
+
+class _CudaBuffer:
+    """__cuda_array_interface__ holder so torch can view a raw device allocation."""
+
+    def __init__(self, ptr, shape):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "<f4", "data": (int(ptr), False),
+                                         "version": 2, "strides": None}
+
+
+class PeerOutput:
+    """C (m x n fp32, row-major) resident on ``root``'s GPU and mapped into every rank of ``group``.
+
+    ``write_slab(mat, d_a, ...)`` runs this rank's product with ``d_c`` pointing into the ROOT's
+    memory at the slab's first column (``ldc = n``): the kernels' epilogues read-modify-write C
+    across NVLink / NVSwitch, so no separate gather follows ("fused alternative").
+    ``finish()`` makes the result visible to the root: every rank synchronises the stream it used,
+    then a barrier.  The root views C as a torch tensor with ``tensor()``.
+
+    One process per GPU; the 64-byte CUDA IPC handle travels through ``broadcast_object_list``."""
+
+    def __init__(self, m, n, root=0, device=0, group=None):
+        import ctypes as C
+
+        import torch.distributed as dist
+
+        from . import _capi
+        self.m, self.n, self.root, self.device, self.group = int(m), int(n), int(root), int(device), group
+        self.rank = dist.get_rank(group)
+        self._lib = _capi.lib()
+        self._owned = self._mapped = None
+        ptr = C.c_void_p()
+        box, err = [None], None
+        if self.rank == self.root:
+            handle = (C.c_uint8 * 64)()
+            try:
+                _capi.check(self._lib.sblas_b200_peer_alloc(self.device, self.m * self.n * 4, C.byref(ptr), handle))
+                self._owned = ptr.value
+                box[0] = bytes(handle)
+            except _capi.SblasError as e:
+                err = str(e)
+        dist.broadcast_object_list(box, src=dist.get_global_rank(group, self.root) if group is not None else self.root,
+                                   group=group)
+        if self.rank != self.root and box[0] is not None:
+            handle = (C.c_uint8 * 64).from_buffer_copy(box[0])
+            try:
+                _capi.check(self._lib.sblas_b200_peer_open(self.device, handle, C.byref(ptr)))
+                self._mapped = ptr.value
+            except _capi.SblasError as e:
+                err = str(e)
+        # success or failure is collective: a rank must not walk on into barriers its peers never reach
+        errs = [None] * dist.get_world_size(group)
+        dist.all_gather_object(errs, err, group=group)
+        if box[0] is None or any(errs):
+            self.base = None
+            self.close()
+            raise RuntimeError("PeerOutput: " + "; ".join(f"rank {r}: {e}" for r, e in enumerate(errs) if e))
+        self.base = ptr.value
+
+    def slab_pointer(self, col_begin):
+        """Device address of C[0][col_begin] as seen from this rank."""
+        return self.base + 4 * int(col_begin)
+
+    def write_slab(self, mat: DeviceMatrix, d_a, lda, col_begin, alpha, beta, stream=0):
+        """C[:, col_begin : col_begin + mat.n] = beta * (same) + alpha * A * S_slab, stored on the root's GPU."""
+        mat.addmatmat_dev(d_a, self.m, lda, self.slab_pointer(col_begin), self.n, alpha, beta, stream=stream)
+
+    def finish(self):
+        import torch
+        import torch.distributed as dist
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=self.group)
+
+    def tensor(self):
+        """The whole C as a torch CUDA tensor (root only; it aliases the allocation, keep ``self`` alive)."""
+        import torch
+        if self.rank != self.root:
+            raise RuntimeError("only the root rank holds C")
+        return torch.as_tensor(_CudaBuffer(self.base, (self.m, self.n)), device=torch.device("cuda", self.device))
+
+    def close(self):
+        """Collective: peers unmap first, then the root frees."""
+        import torch.distributed as dist
+        if self._mapped is not None:
+            self._lib.sblas_b200_peer_close(self._mapped)
+            self._mapped = None
+        dist.barrier(group=self.group)
+        if self._owned is not None:
+            self._lib.sblas_b200_peer_free(self._owned)
+            self._owned = None
+        self.base = None
 
 
 def model_scaling_ceiling(nnz, n, k, m, world_size, bytes_per_nnz=5):

@@ -1,0 +1,103 @@
+// peer_memory.cu -- device allocations another process (one process per GPU) can map, so that a
+// rank's product kernels write their slab of C straight into the memory of the GPU that wants the
+// whole result ("kernel epilogue stores straight into peer-mapped Y").
+//
+// The reference has no counterpart: its panels are independent (sparse-matrix.cc:164-190) and all
+// live in one address space.  Here the output rows of a slab are independent in the same way, so
+// "reassembly" needs no collective at all -- only a C pointer that happens to be NVLink-mapped.
+// The product entry points take it like any other device pointer (c + col_begin, ldc = n).
+//
+// cudaIpc handles are the plumbing: 64 opaque bytes the owner hands to its peers through whatever
+// channel the application has (torch.distributed in sparsematrix_b200/sharding.py).
+#include <string.h>
+
+#include <map>
+
+#include "device_matrix.h"
+
+namespace sblas_b200 {
+namespace {
+std::mutex g_peer_lock;
+std::map<void *, int> g_peer_owned;    // pointer -> device, allocations of sblas_b200_peer_alloc
+std::map<void *, int> g_peer_opened;   // pointer -> device, mappings of sblas_b200_peer_open
+}  // namespace
+}  // namespace sblas_b200
+
+using namespace sblas_b200;
+
+extern "C" {
+
+int sblas_b200_peer_alloc(int32_t device, int64_t bytes, void **d_ptr, uint8_t *handle) {
+    if (!d_ptr || !handle) return fail(SBLAS_B200_EINVAL, "peer_alloc: null output pointer");
+    if (bytes <= 0) return fail(SBLAS_B200_EINVAL, "peer_alloc: bytes = %lld", (long long)bytes);
+    static_assert(sizeof(cudaIpcMemHandle_t) == SBLAS_B200_IPC_HANDLE_BYTES, "handle size is part of the ABI");
+    DeviceScope scope(device);
+    if (!scope.ok()) return SBLAS_B200_ECUDA;
+    void *p = nullptr;
+    cudaError_t e = cudaMalloc(&p, (size_t)bytes);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(SBLAS_B200_ENOMEM, "peer_alloc: cudaMalloc of %lld bytes: %s", (long long)bytes, cudaGetErrorString(e));
+    }
+    cudaIpcMemHandle_t h;
+    e = cudaIpcGetMemHandle(&h, p);
+    if (e != cudaSuccess) {
+        cudaFree(p);
+        return cuda_fail(e, "cudaIpcGetMemHandle", __FILE__, __LINE__);
+    }
+    memcpy(handle, &h, sizeof(h));
+    {
+        std::lock_guard<std::mutex> guard(g_peer_lock);
+        g_peer_owned[p] = device;
+    }
+    *d_ptr = p;
+    return SBLAS_B200_OK;
+}
+
+int sblas_b200_peer_open(int32_t device, const uint8_t *handle, void **d_ptr) {
+    if (!d_ptr || !handle) return fail(SBLAS_B200_EINVAL, "peer_open: null pointer");
+    DeviceScope scope(device);
+    if (!scope.ok()) return SBLAS_B200_ECUDA;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    void *p = nullptr;
+    SB_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    {
+        std::lock_guard<std::mutex> guard(g_peer_lock);
+        g_peer_opened[p] = device;
+    }
+    *d_ptr = p;
+    return SBLAS_B200_OK;
+}
+
+int sblas_b200_peer_close(void *d_ptr) {
+    int device;
+    {
+        std::lock_guard<std::mutex> guard(g_peer_lock);
+        auto it = g_peer_opened.find(d_ptr);
+        if (it == g_peer_opened.end()) return fail(SBLAS_B200_EINVAL, "peer_close: not a pointer of sblas_b200_peer_open");
+        device = it->second;
+        g_peer_opened.erase(it);
+    }
+    DeviceScope scope(device);
+    if (!scope.ok()) return SBLAS_B200_ECUDA;
+    SB_CUDA(cudaIpcCloseMemHandle(d_ptr));
+    return SBLAS_B200_OK;
+}
+
+int sblas_b200_peer_free(void *d_ptr) {
+    int device;
+    {
+        std::lock_guard<std::mutex> guard(g_peer_lock);
+        auto it = g_peer_owned.find(d_ptr);
+        if (it == g_peer_owned.end()) return fail(SBLAS_B200_EINVAL, "peer_free: not a pointer of sblas_b200_peer_alloc");
+        device = it->second;
+        g_peer_owned.erase(it);
+    }
+    DeviceScope scope(device);
+    if (!scope.ok()) return SBLAS_B200_ECUDA;
+    SB_CUDA(cudaFree(d_ptr));
+    return SBLAS_B200_OK;
+}
+
+}  // extern "C"

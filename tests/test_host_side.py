@@ -108,6 +108,15 @@ def test_argument_errors_are_reported_without_a_device():
     assert rc == _capi.EINVAL and b"valid_table_size" in L.sblas_b200_last_error()
     rc = L.sblas_b200_addmatmat_host(None, None, 1, 1, None, 1, 1.0, 1.0)
     assert rc == _capi.EINVAL
+    # peer-visible output: argument checks first, then "no device" -- never a host allocation instead
+    handle = (C.c_uint8 * 64)()
+    assert L.sblas_b200_peer_alloc(0, 0, C.byref(out), handle) == _capi.EINVAL
+    assert L.sblas_b200_peer_alloc(0, 64, None, handle) == _capi.EINVAL
+    assert L.sblas_b200_peer_close(C.c_void_p(1234)) == _capi.EINVAL
+    assert L.sblas_b200_peer_free(C.c_void_p(1234)) == _capi.EINVAL
+    import torch
+    if not torch.cuda.is_available():
+        assert L.sblas_b200_peer_alloc(0, 64, C.byref(out), handle) == _capi.ECUDA
 
 
 def test_save_and_load_round_trip_and_reject_corruption(tmp_path):

@@ -1,0 +1,92 @@
+"""Two GPUs, one process each (NCCL): every rank's product kernels store their slab of C straight
+into rank 0's memory through an NVLink-mapped pointer (sharding.PeerOutput), and the assembled C
+must equal, bit for bit, the all-gather of the slabs computed into local memory -- the kernels
+are the same, only the C pointer differs.  Skipped on a box with one GPU."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, ret):
+    import torch.distributed as dist
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    import sparsematrix_b200 as sb
+    from sparsematrix_b200 import gen, sharding
+
+    n, k = 2048 + 300, 700
+    codes = gen.codes_bernoulli(n, k, 0.08, seed=5)
+    codes[512:768] = 255                                    # an empty panel
+    S = sb.SparseMatrix(codes, n, k, k, gen.codebook(), 255, sb.SparseMatrix.Trans)
+    mat, (lo, hi) = sharding.upload_local_slab(S, rank, world, device=rank)
+    splits = sharding.slab_bounds(S, world)
+    dev = torch.device("cuda", rank)
+    results = []
+    for m, alpha, beta in ((1, 1.0, 1.0), (16, 1.3, 2.0), (128, 1.0, 0.5)):
+        a = torch.from_numpy(gen.dense_uniform((m, k), 10 + m)).to(dev)
+        c0 = torch.from_numpy(gen.dense_uniform((m, n), 20 + m)).to(dev)
+        # (1) local slab + NCCL all-gather
+        c_local = c0[:, lo:hi].contiguous()
+        if mat is not None:
+            mat.addmatmat_dev(a, m, k, c_local, hi - lo, alpha, beta)
+        full_gather = sharding.gather_output(c_local, m, splits)
+        # (2) stores through the peer mapping, no collective on the data path
+        out = sharding.PeerOutput(m, n, root=0, device=rank)
+        if rank == 0:
+            out.tensor().copy_(c0)
+        out.finish()                                        # C initialised before anyone updates it
+        if mat is not None:
+            out.write_slab(mat, a, k, lo, alpha, beta)
+        out.finish()
+        if rank == 0:
+            got = out.tensor().cpu().numpy().view(np.uint32)
+            want = full_gather.cpu().numpy().view(np.uint32)
+            results.append(bool(np.array_equal(got, want)))
+            # and the columns of the empty panel only got the scale
+            ref = (c0[:, 512:768] * beta if beta != 1.0 else c0[:, 512:768]).cpu().numpy().view(np.uint32)
+            results.append(bool(np.array_equal(got.reshape(m, n)[:, 512:768], ref)))
+        out.close()
+    if rank == 0:
+        ret["ok"] = results
+        ret["splits"] = [int(x) for x in splits]
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_peer_mapped_output_equals_allgather_of_local_slabs():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        ret = mgr.dict()
+        port = _free_port()
+        procs = [ctx.Process(target=_worker, args=(r, 2, port, ret)) for r in range(2)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(300)
+        for p in procs:
+            if p.is_alive():
+                p.kill()
+            assert p.exitcode == 0, f"worker exit code {p.exitcode}"
+        assert ret["ok"] and all(ret["ok"]), dict(ret)
+        assert ret["splits"][0] == 0 and ret["splits"][-1] == 2348

@@ -224,6 +224,11 @@ def run_ours(args):
     rank, local_rank, world = dist_env()
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; this library has no CPU fallback")
+    # stdout carries the one JSON line and nothing else: libraries that print there (NCCL's version
+    # banner at N > 1) are sent to stderr for the duration of the run
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
@@ -432,7 +437,8 @@ def run_ours(args):
                     t0 = time.perf_counter(); np.dot(a_h, w.T); t_best = min(t_best, time.perf_counter() - t0)
                 line["cpu_dense_openblas"] = {"value": flops / t_best / 1e9, "unit": "GFLOP/s (sparse flops)", "ms_per_step": t_best * 1e3,
                                               "cores": os.cpu_count(), "what": "numpy.dot (bundled OpenBLAS, all cores) on the dense expansion"}
-        print(json.dumps(line), flush=True)
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

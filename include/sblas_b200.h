@@ -186,8 +186,12 @@ SBLAS_B200_API int sblas_b200_addmatmat_dev(sblas_b200_matrix *mat, const float 
  * ldc = n in sblas_b200_addmatmat_dev().  One process per GPU, so the mapping
  * goes through a CUDA IPC handle (64 opaque bytes, sent by any channel):
  *   _peer_alloc : cudaMalloc on `device` + the handle of that allocation
- *   _peer_open  : map another process's allocation into this process for `device`
- *                 (peer access is enabled on first use); not for the owner itself
+ *   _peer_open  : map another process's allocation of `bytes` bytes into this process
+ *                 for `device` (peer access is enabled on first use); not for the
+ *                 owner itself.  Products whose c lies inside such a mapping skip
+ *                 the L2 prefetch of C and, for beta == 1, add their sums with
+ *                 reductions at the owner's memory instead of reading C over the link
+ *                 (same single rounding; subnormal sums are flushed to zero there)
  *   _peer_close : unmap a pointer of _peer_open
  *   _peer_free  : free a pointer of _peer_alloc (after every peer has closed it)
  * The owner must not read C before the writers' streams have been synchronised
@@ -196,7 +200,7 @@ SBLAS_B200_API int sblas_b200_addmatmat_dev(sblas_b200_matrix *mat, const float 
  */
 #define SBLAS_B200_IPC_HANDLE_BYTES 64
 SBLAS_B200_API int sblas_b200_peer_alloc(int32_t device, int64_t bytes, void **d_ptr, uint8_t *handle);
-SBLAS_B200_API int sblas_b200_peer_open(int32_t device, const uint8_t *handle, void **d_ptr);
+SBLAS_B200_API int sblas_b200_peer_open(int32_t device, const uint8_t *handle, int64_t bytes, void **d_ptr);
 SBLAS_B200_API int sblas_b200_peer_close(void *d_ptr);
 SBLAS_B200_API int sblas_b200_peer_free(void *d_ptr);
 

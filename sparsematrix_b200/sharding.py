@@ -103,7 +103,7 @@ class PeerOutput:
         if self.rank != self.root and box[0] is not None:
             handle = (C.c_uint8 * 64).from_buffer_copy(box[0])
             try:
-                _capi.check(self._lib.sblas_b200_peer_open(self.device, handle, C.byref(ptr)))
+                _capi.check(self._lib.sblas_b200_peer_open(self.device, handle, self.m * self.n * 4, C.byref(ptr)))
                 self._mapped = ptr.value
             except _capi.SblasError as e:
                 err = str(e)

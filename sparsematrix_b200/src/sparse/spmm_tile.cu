@@ -65,6 +65,9 @@ __device__ __forceinline__ unsigned long long gtime() {
 // The warp's quad-row stream goes through a private ring of kRingSegs segments of kSegRows quad rows;
 // a segment is fetched by the warp itself with 16-byte cp.async (LDGSTS) three segments ahead.
 constexpr int kSegRows = 8, kRingSegs = 4;
+// epilogue variants (kernel argument `epi`): C in local memory is prefetched into L2 during the k loop and
+// read-modify-written; C in a peer GPU's memory is not prefetched and, for beta == 1, updated by reductions
+constexpr int kEpiNoPrefetch = 1, kEpiRedAdd = 2;
 constexpr int kSegBytes = kSegRows * kBlockBytes;                // 640
 constexpr int kRingBytes = kRingSegs * kSegBytes;                // 2560 B per warp
 
@@ -168,7 +171,7 @@ __global__ void __maxnreg__((RS == 1 && NF4 == 1) ? 64 : TILE_MAXNREG_BIG)
 spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__ grp_ptr,
                  const uint32_t *__restrict__ grp_nq, const int32_t *__restrict__ row_ptr, int ngroups, int nchunks,
                  int n, const float *__restrict__ xt, int k_alloc, float *__restrict__ c, int ldc, int m, float alpha,
-                 float beta, int nwarps) {
+                 float beta, int nwarps, int epi) {
     constexpr int MT = 32 * NF4 / SPLIT, G = 4 * RS;
     static_assert(SPLIT == 1 || ((SPLIT == 2 || SPLIT == 4) && NF4 == 1), "narrow tiles have one float4 per lane");
     constexpr int STAGE_BYTES = 256 * MT * 4;                    // 255 data rows, padded to a round size
@@ -209,7 +212,7 @@ spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__
         for (int idx = threadIdx.x; idx < nwarps * nchunks; idx += blockDim.x)
             s_nq[idx] = first + idx < limit ? grp_nq[first + idx] : 0u;
         const int lines = (RB + 31) / 32 + 1;                    // 128-byte lines of one C row segment
-        for (int idx = threadIdx.x; idx < MT * lines; idx += blockDim.x) {
+        for (int idx = threadIdx.x; idx < MT * lines && !(epi & kEpiNoPrefetch); idx += blockDim.x) {
             const int i = idx / lines, l = idx - i * lines;
             if (m0 + i < m && j0 + l * 32 < n)
                 asm volatile("prefetch.global.L2 [%0];" ::"l"(c + (size_t)(m0 + i) * ldc + j0 + l * 32));
@@ -325,6 +328,23 @@ spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__
 
     // every warp is past the k loop: the X ring is free, stage the RB x MT result tile in it
     if (threadIdx.x < RB) s_len[threadIdx.x] = my_len;
+    // C[m0+i][j0 .. j0+RB) += tile column i: 128-byte rows along j.  A warp takes kEpi rows of C at a
+    // time and issues all their loads before the first use; the first (normally the only) batch is
+    // issued here, ahead of the two barriers and the staging of the tile, which hide its latency.
+    constexpr int kEpi = NF4 == 2 ? 5 : 4, kJ = kMaxRows / 32;
+    const int nw_all = blockDim.x >> 5;
+    const bool red_add = (epi & kEpiRedAdd) && beta == 1.0f;
+    float c0[kEpi][kJ];
+    auto load_c = [&](int ib) {
+#pragma unroll
+        for (int e = 0; e < kEpi; ++e)
+#pragma unroll
+            for (int u = 0; u < kJ; ++u) {
+                const int jl = lane + 32 * u, i = ib + e;
+                c0[e][u] = (i < MT && m0 + i < m && jl < RB && j0 + jl < n) ? c[(size_t)(m0 + i) * ldc + j0 + jl] : 0.0f;
+            }
+    };
+    if (!red_add) load_c(warp * kEpi);
     __syncthreads();
     TL(5);
     float *tile = reinterpret_cast<float *>(smem_raw);           // [RB][MT + 1]
@@ -348,19 +368,21 @@ spmm_tile_kernel(const uint8_t *__restrict__ blocks, const int32_t *__restrict__
             }
     }
     __syncthreads();
-    // C[m0+i][j0 .. j0+RB) += tile column i: 128-byte rows along j.  A warp takes kEpi rows of C at
-    // a time and issues all their loads before the first use.
-    constexpr int kEpi = 4, kJ = kMaxRows / 32;
-    const int nw_all = blockDim.x >> 5;
-    for (int ib = warp * kEpi; ib < MT && m0 + ib < m; ib += nw_all * kEpi) {
-        float c0[kEpi][kJ];
-#pragma unroll
-        for (int e = 0; e < kEpi; ++e)
+    if (red_add) {
+        // C in a peer GPU's memory: C += sum as a reduction at the memory (red.global.add.f32, one
+        // rounding like the add it replaces), so no read of C crosses the link and nothing waits for one
+        for (int i = warp; i < MT && m0 + i < m; i += nw_all)
 #pragma unroll
             for (int u = 0; u < kJ; ++u) {
-                const int jl = lane + 32 * u, i = ib + e;
-                c0[e][u] = (i < MT && m0 + i < m && jl < RB && j0 + jl < n) ? c[(size_t)(m0 + i) * ldc + j0 + jl] : 0.0f;
+                const int jl = lane + 32 * u;
+                if (jl < RB && j0 + jl < n && s_len[jl])
+                    asm volatile("red.global.add.f32 [%0], %1;" ::"l"(c + (size_t)(m0 + i) * ldc + j0 + jl),
+                                 "f"(tile[(size_t)jl * (MT + 1) + i]) : "memory");
             }
+        return;
+    }
+    for (int ib = warp * kEpi; ib < MT && m0 + ib < m; ib += nw_all * kEpi) {
+        if (ib != warp * kEpi) load_c(ib);
 #pragma unroll
         for (int e = 0; e < kEpi; ++e)
 #pragma unroll
@@ -397,7 +419,7 @@ static void dump_timeline() {
 
 template <int RS, int NF4, int STAGES, int SPLIT = 1>
 static int launch_tile(const sblas_b200_matrix *mat, const TileFormat &tf, const float *xt, int k_alloc, float *d_c,
-                       int ldc, int m, float alpha, float beta, int nwarps, cudaStream_t stream) {
+                       int ldc, int m, float alpha, float beta, int nwarps, int epi, cudaStream_t stream) {
     constexpr int MT = 32 * NF4 / SPLIT, MAXW = kMaxRows / (4 * RS);
     const int nchunks = tf.nchunks;
     auto smem_for = [nchunks](int nw) { return (size_t)STAGES * 256 * MT * 4 + (size_t)nw * kRingBytes + 2 * STAGES * 8 + (size_t)nw * nchunks * 4; };
@@ -430,7 +452,7 @@ static int launch_tile(const sblas_b200_matrix *mat, const TileFormat &tf, const
     auto kernel = alpha == 1.0f ? spmm_tile_kernel<RS, NF4, STAGES, false, SPLIT> : spmm_tile_kernel<RS, NF4, STAGES, true, SPLIT>;
     SB_CUDA(cudaLaunchKernelEx(&cfg, kernel, (const uint8_t *)tf.d_blocks, (const int32_t *)tf.d_grp_ptr,
                                (const uint32_t *)tf.d_grp_nq, (const int32_t *)mat->d_row_ptr, ngroups, nchunks, n, xt,
-                               k_alloc, d_c, ldc, m, alpha, beta, nwarps));
+                               k_alloc, d_c, ldc, m, alpha, beta, nwarps, epi));
     g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
     SB_CHECK_LAUNCH();
     return SBLAS_B200_OK;
@@ -510,14 +532,19 @@ int run_spmm_tile(sblas_b200_matrix *mat, const float *d_a, int m, int lda, floa
         ~Timer() { if (a) { cudaEventRecord(b, st); mat->prof_events.push_back(std::make_pair(a, b)); } }
     } timer(mat, stream);
     const float *xt = mat->d_ws;
-    if (plan.split == 4 && plan.rs == 1) return launch_tile<1, 1, 4, 4>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, stream);
-    if (plan.split == 4) return launch_tile<2, 1, 4, 4>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, stream);
-    if (plan.split == 2 && plan.rs == 1) return launch_tile<1, 1, 4, 2>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, stream);
-    if (plan.split == 2) return launch_tile<2, 1, 4, 2>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, stream);
-    if (plan.rs == 1 && plan.nf4 == 1) return launch_tile<1, 1, 3>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, stream);
-    if (plan.rs == 1) return launch_tile<1, 2, 2>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, stream);
-    if (plan.nf4 == 1) return launch_tile<2, 1, 3>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, stream);
-    return launch_tile<2, 2, 2>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, stream);
+    // where C lives decides the epilogue: a pointer into another GPU's memory (sblas_b200_peer_open) is
+    // neither prefetched nor read when beta == 1.  SBLAS_B200_EPI overrides (experiments).
+    static const int env_epi = [] { const char *e = getenv("SBLAS_B200_EPI"); return (e && *e) ? atoi(e) : -1; }();
+    int epi = env_epi;
+    if (epi < 0) epi = is_peer_pointer(d_c) ? (kEpiNoPrefetch | kEpiRedAdd) : 0;
+    if (plan.split == 4 && plan.rs == 1) return launch_tile<1, 1, 4, 4>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, epi, stream);
+    if (plan.split == 4) return launch_tile<2, 1, 4, 4>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, epi, stream);
+    if (plan.split == 2 && plan.rs == 1) return launch_tile<1, 1, 4, 2>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, epi, stream);
+    if (plan.split == 2) return launch_tile<2, 1, 4, 2>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, epi, stream);
+    if (plan.rs == 1 && plan.nf4 == 1) return launch_tile<1, 1, 3>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, epi, stream);
+    if (plan.rs == 1) return launch_tile<1, 2, 2>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, epi, stream);
+    if (plan.nf4 == 1) return launch_tile<2, 1, 3>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, epi, stream);
+    return launch_tile<2, 2, 2>(mat, tf, xt, k_alloc, d_c, ldc, m, alpha, beta, plan.nwarps, epi, stream);
 }
 
 }  // namespace sblas_b200

@@ -142,6 +142,8 @@ namespace sblas_b200 {
 int plan_spmv(sblas_b200_matrix *mat, const int32_t *h_row_ptr);
 int ensure_buffer(float **buf, size_t *have, size_t need);
 int exclusive_scan_i32(const int32_t *d_in, int n, int32_t *d_out, cudaStream_t stream);   // d_out[n] = total
+// src/utils/peer_memory.cu: does p point into a mapping made by sblas_b200_peer_open (another GPU's memory)?
+bool is_peer_pointer(const void *p);
 // src/utils/tile_format.cu
 constexpr int kTileK = 255;          // X rows per chunk; offset 255 addresses an all-zero row (padding entries)
 constexpr int kBlockBytes = 80;

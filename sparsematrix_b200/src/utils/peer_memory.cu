@@ -19,8 +19,20 @@ namespace sblas_b200 {
 namespace {
 std::mutex g_peer_lock;
 std::map<void *, int> g_peer_owned;    // pointer -> device, allocations of sblas_b200_peer_alloc
-std::map<void *, int> g_peer_opened;   // pointer -> device, mappings of sblas_b200_peer_open
+struct Mapping { size_t bytes; int device; };
+std::map<uintptr_t, Mapping> g_peer_opened;   // base -> extent, mappings of sblas_b200_peer_open
+std::atomic<int> g_peer_open_count{0};
 }  // namespace
+
+bool is_peer_pointer(const void *p) {
+    if (g_peer_open_count.load(std::memory_order_relaxed) == 0) return false;   // the common case costs one load
+    const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+    std::lock_guard<std::mutex> guard(g_peer_lock);
+    auto it = g_peer_opened.upper_bound(a);
+    if (it == g_peer_opened.begin()) return false;
+    --it;
+    return a - it->first < it->second.bytes;
+}
 }  // namespace sblas_b200
 
 using namespace sblas_b200;
@@ -54,8 +66,9 @@ int sblas_b200_peer_alloc(int32_t device, int64_t bytes, void **d_ptr, uint8_t *
     return SBLAS_B200_OK;
 }
 
-int sblas_b200_peer_open(int32_t device, const uint8_t *handle, void **d_ptr) {
+int sblas_b200_peer_open(int32_t device, const uint8_t *handle, int64_t bytes, void **d_ptr) {
     if (!d_ptr || !handle) return fail(SBLAS_B200_EINVAL, "peer_open: null pointer");
+    if (bytes <= 0) return fail(SBLAS_B200_EINVAL, "peer_open: bytes = %lld", (long long)bytes);
     DeviceScope scope(device);
     if (!scope.ok()) return SBLAS_B200_ECUDA;
     cudaIpcMemHandle_t h;
@@ -64,7 +77,8 @@ int sblas_b200_peer_open(int32_t device, const uint8_t *handle, void **d_ptr) {
     SB_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
     {
         std::lock_guard<std::mutex> guard(g_peer_lock);
-        g_peer_opened[p] = device;
+        g_peer_opened[reinterpret_cast<uintptr_t>(p)] = Mapping{(size_t)bytes, device};
+        g_peer_open_count.fetch_add(1, std::memory_order_relaxed);
     }
     *d_ptr = p;
     return SBLAS_B200_OK;
@@ -74,10 +88,11 @@ int sblas_b200_peer_close(void *d_ptr) {
     int device;
     {
         std::lock_guard<std::mutex> guard(g_peer_lock);
-        auto it = g_peer_opened.find(d_ptr);
+        auto it = g_peer_opened.find(reinterpret_cast<uintptr_t>(d_ptr));
         if (it == g_peer_opened.end()) return fail(SBLAS_B200_EINVAL, "peer_close: not a pointer of sblas_b200_peer_open");
-        device = it->second;
+        device = it->second.device;
         g_peer_opened.erase(it);
+        g_peer_open_count.fetch_sub(1, std::memory_order_relaxed);
     }
     DeviceScope scope(device);
     if (!scope.ok()) return SBLAS_B200_ECUDA;

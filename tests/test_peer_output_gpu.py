@@ -1,7 +1,9 @@
 """Two GPUs, one process each (NCCL): every rank's product kernels store their slab of C straight
 into rank 0's memory through an NVLink-mapped pointer (sharding.PeerOutput), and the assembled C
 must equal, bit for bit, the all-gather of the slabs computed into local memory -- the kernels
-are the same, only the C pointer differs.  Skipped on a box with one GPU."""
+are the same, only the C pointer differs (for beta == 1 the SpMM tile kernel adds into peer memory
+with red.global.add.f32 instead of a read-modify-write: same single rounding, cases m = 64 and 8).
+Skipped on a box with one GPU."""
 import os
 import socket
 import sys
@@ -41,11 +43,11 @@ def _worker(rank, world, port, ret):
     splits = sharding.slab_bounds(S, world)
     dev = torch.device("cuda", rank)
     results = []
-    for m, alpha, beta in ((1, 1.0, 1.0), (16, 1.3, 2.0), (128, 1.0, 0.5)):
+    for m, alpha, beta in ((1, 1.0, 1.0), (16, 1.3, 2.0), (128, 1.0, 0.5), (64, 1.0, 1.0), (8, 1.7, 1.0)):
         a = torch.from_numpy(gen.dense_uniform((m, k), 10 + m)).to(dev)
         c0 = torch.from_numpy(gen.dense_uniform((m, n), 20 + m)).to(dev)
         # (1) local slab + NCCL all-gather
-        c_local = c0[:, lo:hi].contiguous()
+        c_local = c0[:, lo:hi].clone()                   # (.contiguous() of a one-row slice is a view of c0)
         if mat is not None:
             mat.addmatmat_dev(a, m, k, c_local, hi - lo, alpha, beta)
         full_gather = sharding.gather_output(c_local, m, splits)

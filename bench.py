@@ -303,8 +303,13 @@ def run_ours(args):
 
     # end to end through the reference-facing host entry point: pinned host buffers,
     # H2D of A and C, kernels, D2H of C inside every timed step
-    h_a = torch.from_numpy(inp["a"]).pin_memory()
-    h_c = torch.zeros((m, n), dtype=torch.float32).pin_memory()
+    # the caller's buffers come from the library's own allocator (sblas_b200_host_alloc = cudaHostAlloc, mapped):
+    # torch's pin_memory() blocks copy at 10-25 GB/s instead of 50 on some allocations of this VM
+    # (tools/microbench/numa_probe.py, zero_copy_bench.cu; profiles/r01d_e2e.md)
+    h_a = sb.host_buffer((m, k))
+    h_a[...] = inp["a"]
+    h_c = sb.host_buffer((m, n))
+    h_c[...] = 0.0
     e2e_steps = max(3, min(args.steps, 50))
     for _ in range(3):
         mat.addmatmat_host(h_a, m, k, h_c, n, 1.0, 1.0)
@@ -393,7 +398,7 @@ def run_ours(args):
             "e2e": {"value": world * flops / (e2e_ms / e2e_steps * 1e-3) / 1e9, "unit": "GFLOP/s",
                     "h2d_bytes_per_step": int(4 * m * (k + n)), "d2h_bytes_per_step": int(4 * m * n),
                     "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps,
-                    "api": "sblas_b200_addmatmat_host (pinned host A, C; synchronous)", "checksum": checksum},
+                    "api": "sblas_b200_addmatmat_host (host A, C from sblas_b200_host_alloc: page-locked + mapped; synchronous)", "checksum": checksum},
             "gpu_launches": int(launches), "clocks": clocks.summary(),
         }
         # what actually bounds the kernel; `frac` above stays the HBM fraction the contract asks for

@@ -177,6 +177,16 @@ SBLAS_B200_API int sblas_b200_addmatmat_host(sblas_b200_matrix *mat, const float
 SBLAS_B200_API int sblas_b200_addmatmat_dev(sblas_b200_matrix *mat, const float *d_a, int32_t m, int32_t lda,
                                             float *d_c, int32_t ldc, float alpha, float beta, void *stream);
 
+/*
+ * Page-locked, device-mapped host memory for the caller's a and c.  Any host
+ * pointer works with sblas_b200_addmatmat_host(); with memory of this kind
+ * (these calls, cudaHostAlloc or cudaHostRegister) the copies run beside the
+ * product and the result is written straight into c.  Fails with
+ * SBLAS_B200_ECUDA without a device: there is no malloc fallback.
+ */
+SBLAS_B200_API int sblas_b200_host_alloc(int64_t bytes, void **ptr);
+SBLAS_B200_API int sblas_b200_host_free(void *ptr);
+
 /* ---- peer-visible output: reassembly across GPUs without a collective ------ */
 /*
  * The slabs of sblas_b200_upload_slab() write disjoint column ranges of C (the

@@ -51,6 +51,8 @@ SYMBOLS = {
     "sblas_b200_copyform_begin": (C.c_int, [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _vp, _vp]),
     "sblas_b200_copyform_finish": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "sblas_b200_copyform_abort": (None, [_vp]),
+    "sblas_b200_host_alloc": (C.c_int, [_i64, _vp]),
+    "sblas_b200_host_free": (C.c_int, [_vp]),
     "sblas_b200_peer_alloc": (C.c_int, [_i32, _i64, _vp, _vp]),
     "sblas_b200_peer_open": (C.c_int, [_i32, _vp, _i64, _vp]),
     "sblas_b200_peer_close": (C.c_int, [_vp]),

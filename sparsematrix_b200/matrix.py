@@ -48,6 +48,32 @@ def _f32c(a):
     return a
 
 
+class _PinnedBlock:
+    """Owner of one sblas_b200_host_alloc() block; freed when the last array over it goes away."""
+
+    def __init__(self, nbytes):
+        p = C.c_void_p()
+        _capi.check(_capi.lib().sblas_b200_host_alloc(nbytes, C.byref(p)))
+        self.ptr, self.nbytes = p.value, nbytes
+
+    def __del__(self):
+        try:
+            _capi.lib().sblas_b200_host_free(C.c_void_p(self.ptr))
+        except Exception:
+            pass
+
+
+def host_buffer(shape, dtype=np.float32):
+    """numpy array over page-locked, device-mapped host memory (``sblas_b200_host_alloc``): the kind of
+    caller buffer for which ``AddMatMat`` / ``addmatmat_host`` overlap the copies with the product."""
+    shape = (shape,) if isinstance(shape, int) else tuple(shape)
+    nbytes = max(1, int(np.prod(shape)) * np.dtype(dtype).itemsize)
+    block = _PinnedBlock(nbytes)
+    raw = (C.c_uint8 * nbytes).from_address(block.ptr)
+    raw._owner = block                                   # numpy keeps `raw` as the array's base, `raw` keeps the block
+    return np.frombuffer(raw, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+
+
 class DeviceMatrix:
     """W = S^T resident on one GPU (opaque sblas_b200_matrix)."""
 

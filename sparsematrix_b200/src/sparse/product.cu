@@ -57,6 +57,9 @@ spmv_rows_kernel(const int32_t *__restrict__ row_ptr, const int4 *__restrict__ c
     __syncthreads();
     const int len = e - s;
     const bool mine = row < n && len <= long_threshold;
+    // the value this row updates is asked for now, so that its round trip overlaps the walk
+    float c0 = 0.0f;
+    if (mine && sub == 0 && !(len == 0 && beta == 1.0f)) c0 = y[row];
     float acc = 0.0f;
     if (mine && len > 0) {
         const int b1 = (e - 1) >> 2;
@@ -82,7 +85,6 @@ spmv_rows_kernel(const int32_t *__restrict__ row_ptr, const int4 *__restrict__ c
     for (int o = LPR >> 1; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     if (mine && sub == 0) {
         if (len == 0 && beta == 1.0f) return;           // column without entries, no scale: untouched
-        float c0 = y[row];
         if (beta != 1.0f) c0 *= beta;
         y[row] = len ? c0 + acc : c0;                   // no entry: exactly the scaled value (keeps -0)
     }
@@ -104,6 +106,8 @@ spmv_sorted_kernel(const int32_t *__restrict__ blk_ptr, const int32_t *__restric
     if (i < n_ordered) { b0 = blk_ptr[i]; len = slen[i]; row = order[i]; }
     s_tab[threadIdx.x] = (threadIdx.x < T) ? table[threadIdx.x] * alpha : 0.0f;    // val_table[code]*alpha
     __syncthreads();
+    float c0 = 0.0f;                                        // asked for now: the round trip overlaps the walk
+    if (i < n_ordered && sub == 0 && !(len == 0 && beta == 1.0f)) c0 = y[row];
     float acc = 0.0f;
     const int nfull = len >> 2, tail = len & 3;
     for (int b = sub; b < nfull; b += LPR) {
@@ -126,7 +130,6 @@ spmv_sorted_kernel(const int32_t *__restrict__ blk_ptr, const int32_t *__restric
     for (int o = LPR >> 1; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     if (i < n_ordered && sub == 0) {
         if (len == 0 && beta == 1.0f) return;               // column without entries, no scale: untouched
-        float c0 = y[row];
         if (beta != 1.0f) c0 *= beta;
         y[row] = len ? c0 + acc : c0;                       // no entry: exactly the scaled value (keeps -0)
     }
@@ -487,6 +490,14 @@ combine_out_kernel(const float *__restrict__ c_in, float *__restrict__ p, const 
     }
 }
 
+// A strided copy whose rows touch is one plain copy: a single DMA descriptor instead of one per row.
+static cudaError_t copy_rows(void *dst, size_t dpitch, const void *src, size_t spitch, size_t width, size_t height,
+                             cudaMemcpyKind kind, cudaStream_t stream) {
+    static const bool force_2d = [] { const char *e = getenv("SBLAS_B200_COPY2D"); return e && *e == '1'; }();   // A/B switch
+    if (dpitch == width && spitch == width && !force_2d) return cudaMemcpyAsync(dst, src, width * height, kind, stream);
+    return cudaMemcpy2DAsync(dst, dpitch, src, spitch, width, height, kind, stream);
+}
+
 // device alias of a pinned + mapped host pointer, or null (pageable memory, or SBLAS_B200_HOST_OVERLAP=0)
 static float *mapped_pointer(const void *host) {
     static const int enabled = [] { const char *e = getenv("SBLAS_B200_HOST_OVERLAP"); return e ? atoi(e) : 1; }();
@@ -545,9 +556,9 @@ static int host_product_overlapped(sblas_b200_matrix *mat, const float *a, int m
     auto copy_in = [&](bool is_a, int s) -> cudaError_t {
         const int i0 = s * rows, mi = std::min(rows, m - i0);
         cudaError_t e = is_a
-            ? cudaMemcpy2DAsync(mat->d_host_a + (size_t)i0 * k, (size_t)k * 4, a + (size_t)i0 * lda, (size_t)lda * 4,
+            ? copy_rows(mat->d_host_a + (size_t)i0 * k, (size_t)k * 4, a + (size_t)i0 * lda, (size_t)lda * 4,
                                 (size_t)k * 4, mi, cudaMemcpyHostToDevice, mat->stream2)
-            : cudaMemcpy2DAsync(mat->d_host_c + (size_t)i0 * n, (size_t)n * 4, c + (size_t)i0 * ldc, (size_t)ldc * 4,
+            : copy_rows(mat->d_host_c + (size_t)i0 * n, (size_t)n * 4, c + (size_t)i0 * ldc, (size_t)ldc * 4,
                                 (size_t)n * 4, mi, cudaMemcpyHostToDevice, mat->stream2);
         if (e == cudaSuccess) e = cudaEventRecord(mat->host_events[3 * s + (is_a ? 0 : 1)], mat->stream2);
         return e;
@@ -582,7 +593,7 @@ static int host_product_overlapped(sblas_b200_matrix *mat, const float *a, int m
             e = cudaEventRecord(mat->host_events[3 * s + 2], mat->stream);
             if (e == cudaSuccess) e = cudaStreamWaitEvent(mat->stream3, mat->host_events[3 * s + 2], 0);
             if (e == cudaSuccess)
-                e = cudaMemcpy2DAsync(c + (size_t)i0 * ldc, (size_t)ldc * 4, cs, (size_t)n * 4, (size_t)n * 4, mi,
+                e = copy_rows(c + (size_t)i0 * ldc, (size_t)ldc * 4, cs, (size_t)n * 4, (size_t)n * 4, mi,
                                       cudaMemcpyDeviceToHost, mat->stream3);
         }
         if (e != cudaSuccess) return fail_sync(cuda_fail(e, "host path combine / copy out", __FILE__, __LINE__));
@@ -661,13 +672,13 @@ int sblas_b200_addmatmat_host(sblas_b200_matrix *mat, const float *a, int32_t m,
     if (c_mapped) return host_product_overlapped(mat, a, m, lda, c, c_mapped, ldc, alpha, beta);
     // pageable caller memory (or scale only): copies and kernels back to back on one stream
     if (need_a)
-        SB_CUDA(cudaMemcpy2DAsync(mat->d_host_a, (size_t)k * 4, a, (size_t)lda * 4, (size_t)k * 4, m,
+        SB_CUDA(copy_rows(mat->d_host_a, (size_t)k * 4, a, (size_t)lda * 4, (size_t)k * 4, m,
                                   cudaMemcpyHostToDevice, mat->stream));
-    SB_CUDA(cudaMemcpy2DAsync(mat->d_host_c, (size_t)n * 4, c, (size_t)ldc * 4, (size_t)n * 4, m,
+    SB_CUDA(copy_rows(mat->d_host_c, (size_t)n * 4, c, (size_t)ldc * 4, (size_t)n * 4, m,
                               cudaMemcpyHostToDevice, mat->stream));
     rc = product_on_stream(mat, mat->d_host_a, m, k, mat->d_host_c, n, alpha, beta, mat->stream);
     if (rc != SBLAS_B200_OK) return rc;
-    SB_CUDA(cudaMemcpy2DAsync(c, (size_t)ldc * 4, mat->d_host_c, (size_t)n * 4, (size_t)n * 4, m,
+    SB_CUDA(copy_rows(c, (size_t)ldc * 4, mat->d_host_c, (size_t)n * 4, (size_t)n * 4, m,
                               cudaMemcpyDeviceToHost, mat->stream));
     SB_CUDA(cudaStreamSynchronize(mat->stream));
     return SBLAS_B200_OK;

@@ -299,6 +299,24 @@ def test_cpp_harness_binaries(binary, expect):
     assert out.returncode == 0 and expect in out.stdout, out.stdout[-2000:] + out.stderr[-500:]
 
 
+# ------------------------------------------------------------------ host entry point, buffers of the library's allocator
+def test_host_alloc_buffers_take_the_overlapped_route_with_the_same_bits():
+    n, k, m = 1500, 900, 33
+    codes = gen.codes_bernoulli(n, k, 0.07, seed=41)
+    S = sb.SparseMatrix(codes, n, k, k, gen.codebook(), 255, 1)
+    a = gen.dense_uniform((m, k), 1); c0 = gen.dense_uniform((m, n), 2)
+    want = S.AddMatMat(a, m, k, c0.copy(), n, 1.3, 0.7)                 # pageable numpy buffers
+    ha = sb.host_buffer((m, k)); hc = sb.host_buffer((m, n))
+    ha[...] = a; hc[...] = c0
+    S.AddMatMat(ha, m, k, hc, n, 1.3, 0.7)
+    assert_bits_equal(hc, want, "sblas_b200_host_alloc buffers vs pageable")
+    hc2 = sb.host_buffer((m, n + 8))                                    # ldc > n: the padding stays untouched
+    hc2[...] = 7.0; hc2[:, :n] = c0
+    S.AddMatMat(ha, m, k, hc2, n + 8, 1.3, 0.7)
+    assert_bits_equal(hc2[:, :n], want, "host_alloc buffer with ldc > n")
+    assert np.all(hc2[:, n:] == 7.0)
+
+
 # ------------------------------------------------------------------ host entry point, pinned caller buffers
 def test_pinned_host_buffers_give_the_same_bits_as_pageable_ones():
     """Pinned A/C take the overlapped route (product into a side buffer while C travels in, one

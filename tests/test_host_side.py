@@ -117,6 +117,9 @@ def test_argument_errors_are_reported_without_a_device():
     import torch
     if not torch.cuda.is_available():
         assert L.sblas_b200_peer_alloc(0, 64, C.byref(out), handle) == _capi.ECUDA
+        assert L.sblas_b200_host_alloc(64, C.byref(out)) == _capi.ECUDA      # no malloc in disguise
+    assert L.sblas_b200_host_alloc(0, C.byref(out)) == _capi.EINVAL
+    assert L.sblas_b200_host_free(None) == _capi.OK
 
 
 def test_save_and_load_round_trip_and_reject_corruption(tmp_path):

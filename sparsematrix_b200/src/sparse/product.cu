@@ -551,6 +551,17 @@ static int host_product_overlapped(sblas_b200_matrix *mat, const float *a, int m
         SB_CHECK_LAUNCH();
     }
     mat->host_p_clean = false;                          // until every combine kernel of this call has run
+    // SBLAS_B200_HOST_TRACE=1: device-side timeline of this call (events on the three streams), printed to stderr
+    static const bool trace = [] { const char *e = getenv("SBLAS_B200_HOST_TRACE"); return e && *e == '1'; }();
+    std::vector<std::pair<const char *, cudaEvent_t> > marks;
+    auto mark = [&](const char *what, cudaStream_t st) {
+        if (!trace) return;
+        cudaEvent_t ev;
+        cudaEventCreate(&ev);
+        cudaEventRecord(ev, st);
+        marks.push_back(std::make_pair(what, ev));
+    };
+    mark("start", mat->stream2);
     auto fail_sync = [&](int code) { cudaStreamSynchronize(mat->stream2); cudaStreamSynchronize(mat->stream3);
                                      cudaStreamSynchronize(mat->stream); return code; };
     auto copy_in = [&](bool is_a, int s) -> cudaError_t {
@@ -561,6 +572,7 @@ static int host_product_overlapped(sblas_b200_matrix *mat, const float *a, int m
             : copy_rows(mat->d_host_c + (size_t)i0 * n, (size_t)n * 4, c + (size_t)i0 * ldc, (size_t)ldc * 4,
                                 (size_t)n * 4, mi, cudaMemcpyHostToDevice, mat->stream2);
         if (e == cudaSuccess) e = cudaEventRecord(mat->host_events[3 * s + (is_a ? 0 : 1)], mat->stream2);
+        mark(is_a ? "A slice in" : "C slice in", mat->stream2);
         return e;
     };
     // copy engine order: A0, A1, C0, A2, C1, ... -- the next product's input before this one's C
@@ -578,6 +590,7 @@ static int host_product_overlapped(sblas_b200_matrix *mat, const float *a, int m
         if (e != cudaSuccess) return fail_sync(cuda_fail(e, "host path wait A", __FILE__, __LINE__));
         rc = product_on_stream(mat, mat->d_host_a + (size_t)i0 * k, mi, k, p, n, alpha, 1.0f, mat->stream);
         if (rc != SBLAS_B200_OK) return fail_sync(rc);
+        mark("product done", mat->stream);
         e = cudaStreamWaitEvent(mat->stream, mat->host_events[3 * s + 1], 0);
         if (e != cudaSuccess) return fail_sync(cuda_fail(e, "host path wait C", __FILE__, __LINE__));
         float *out = direct ? c_mapped : cs;
@@ -589,17 +602,29 @@ static int host_product_overlapped(sblas_b200_matrix *mat, const float *a, int m
         if (vec) SB_LAUNCH(combine_out_kernel<true>, grid, 256, 0, mat->stream, cs, p, mat->d_row_ptr, out, ldo, mi, n, beta);
         else SB_LAUNCH(combine_out_kernel<false>, grid, 256, 0, mat->stream, cs, p, mat->d_row_ptr, out, ldo, mi, n, beta);
         e = cudaGetLastError();
+        mark("combine done", mat->stream);
         if (e == cudaSuccess && !direct) {
             e = cudaEventRecord(mat->host_events[3 * s + 2], mat->stream);
             if (e == cudaSuccess) e = cudaStreamWaitEvent(mat->stream3, mat->host_events[3 * s + 2], 0);
             if (e == cudaSuccess)
                 e = copy_rows(c + (size_t)i0 * ldc, (size_t)ldc * 4, cs, (size_t)n * 4, (size_t)n * 4, mi,
                                       cudaMemcpyDeviceToHost, mat->stream3);
+            mark("slice out", mat->stream3);
         }
         if (e != cudaSuccess) return fail_sync(cuda_fail(e, "host path combine / copy out", __FILE__, __LINE__));
     }
     SB_CUDA(cudaStreamSynchronize(mat->stream));
     if (!direct) SB_CUDA(cudaStreamSynchronize(mat->stream3));
+    if (trace) {
+        fprintf(stderr, "host path m=%d slices=%d:", m, slices);
+        for (size_t i = 1; i < marks.size(); ++i) {
+            float ms = 0.0f;
+            cudaEventElapsedTime(&ms, marks[0].second, marks[i].second);
+            fprintf(stderr, " [%s %.1f us]", marks[i].first, ms * 1e3f);
+        }
+        fprintf(stderr, "\n");
+        for (auto &mk : marks) cudaEventDestroy(mk.second);
+    }
     mat->host_p_clean = true;
     return SBLAS_B200_OK;
 }

@@ -171,7 +171,11 @@ SBLAS_B200_API int sblas_b200_addmatmat_host(sblas_b200_matrix *mat, const float
  * the timed path.  Calls on one handle may come from several threads and
  * streams: the handle's workspace is shared, so a product enqueued on another
  * stream than the previous one is ordered after it with an event (products on
- * different handles run concurrently).  With pinned host buffers
+ * different handles run concurrently).  The call can be recorded into a CUDA
+ * graph (stream capture) once each shape has been run eagerly -- workspaces are
+ * then allocated and no allocation or synchronisation happens inside; replays of
+ * such a graph and other products on the same handle must be ordered by the
+ * caller, the library's event cannot cross a capture.  With pinned host buffers
  * sblas_b200_addmatmat_host() overlaps its copies with the product.
  */
 SBLAS_B200_API int sblas_b200_addmatmat_dev(sblas_b200_matrix *mat, const float *d_a, int32_t m, int32_t lda,

@@ -417,11 +417,19 @@ int product_on_stream(sblas_b200_matrix *mat, const float *d_a, int32_t m, int32
         return SBLAS_B200_OK;
     }
     // Xt staging and split-row partials belong to the handle: order this product after the previous one
-    // when that ran on a different stream
-    if (!mat->ws_event) SB_CUDA(cudaEventCreateWithFlags(&mat->ws_event, cudaEventDisableTiming));
-    if (mat->ws_used && mat->ws_stream != stream) SB_CUDA(cudaStreamWaitEvent(stream, mat->ws_event, 0));
+    // when that ran on a different stream.  Not while `stream` is being captured into a CUDA graph: a
+    // capture may neither wait for work outside it nor lend its events to streams outside it; products
+    // inside one capture are ordered by the capture itself, and keeping replays of the graph apart from
+    // other products of the same handle is then the caller's business (include/sblas_b200.h).
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(stream, &cap) != cudaSuccess) { cudaGetLastError(); cap = cudaStreamCaptureStatusNone; }
+    const bool capturing = cap != cudaStreamCaptureStatusNone;
+    if (!capturing) {
+        if (!mat->ws_event) SB_CUDA(cudaEventCreateWithFlags(&mat->ws_event, cudaEventDisableTiming));
+        if (mat->ws_used && mat->ws_stream != stream) SB_CUDA(cudaStreamWaitEvent(stream, mat->ws_event, 0));
+    }
     const int rc = m == 1 ? run_spmv(mat, d_a, d_c, alpha, beta, stream) : run_spmm(mat, d_a, m, lda, d_c, ldc, alpha, beta, stream);
-    if (rc == SBLAS_B200_OK) {
+    if (rc == SBLAS_B200_OK && !capturing) {
         SB_CUDA(cudaEventRecord(mat->ws_event, stream));
         mat->ws_stream = stream;
         mat->ws_used = true;

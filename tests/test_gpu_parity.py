@@ -668,3 +668,50 @@ def test_narrow_tiles_for_small_m_on_a_large_matrix():
     full = dev.addmatmat_host(a, 8, k, c0.copy(), n, 1.0, 1.0)
     part = dev.addmatmat_host(a[2:5], 3, k, c0[2:5].copy(), n, 1.0, 1.0)
     assert_bits_equal(part, full[2:5], "m = 3 vs rows 2..4 of m = 8 (same 8-column tile)")
+
+
+# ------------------------------------------------------------------ batched small-m calls in a CUDA graph
+def test_products_can_be_captured_into_a_cuda_graph_and_replayed():
+    # A caller with many small products (m = 1 .. 8: launch bound, a few us each) records them once into a
+    # CUDA graph and replays the whole batch with one launch.  The device entry point must therefore be
+    # capturable after one warm-up call per shape (workspaces allocated, kernels configured): no allocation,
+    # no synchronisation, no host-side state that a replay would miss.  Results: bit-identical to eager calls.
+    import torch
+    n, k = 3000, 1100
+    codes = gen.codes_bernoulli(n, k, 0.05, seed=91)
+    S = sb.SparseMatrix(codes, n, k, k, gen.codebook(), 255, 1)
+    dev = S.device_matrix()
+    cuda = torch.device("cuda", 0)
+    ms = (1, 3, 8, 40)
+    a = {m: torch.from_numpy(gen.dense_uniform((m, k), 100 + m)).to(cuda) for m in ms}
+    c0 = {m: torch.from_numpy(gen.dense_uniform((m, n), 200 + m)).to(cuda) for m in ms}
+    want = {}
+    for m in ms:                                        # eager: also the warm-up of every shape
+        c = c0[m].clone()
+        dev.addmatmat_dev(a[m], m, k, c, n, 1.3, 0.7)
+        dev.addmatmat_dev(a[m], m, k, c, n, 1.0, 1.0)
+        torch.cuda.synchronize()
+        want[m] = c.cpu().numpy()
+    c = {m: c0[m].clone() for m in ms}
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    graph = torch.cuda.CUDAGraph()
+    launches0 = sb.lib().sblas_b200_launch_count()
+    with torch.cuda.graph(graph, stream=side):
+        for m in ms:
+            dev.addmatmat_dev(a[m], m, k, c[m], n, 1.3, 0.7, stream=side.cuda_stream)
+            dev.addmatmat_dev(a[m], m, k, c[m], n, 1.0, 1.0, stream=side.cuda_stream)
+    assert sb.lib().sblas_b200_launch_count() > launches0
+    for rep in range(2):
+        for m in ms:
+            c[m].copy_(c0[m])
+        graph.replay()
+        torch.cuda.synchronize()
+        for m in ms:
+            assert_bits_equal(c[m].cpu().numpy(), want[m], f"graph replay {rep} m={m}")
+    # and the handle still works eagerly afterwards, on another stream
+    c1 = c0[8].clone()
+    dev.addmatmat_dev(a[8], 8, k, c1, n, 1.3, 0.7)
+    dev.addmatmat_dev(a[8], 8, k, c1, n, 1.0, 1.0)
+    torch.cuda.synchronize()
+    assert_bits_equal(c1.cpu().numpy(), want[8], "eager after capture")

@@ -343,6 +343,9 @@ static void launch_spmv_rows(const sblas_b200_matrix *mat, const float *x, float
 }
 
 static int run_spmv(sblas_b200_matrix *mat, const float *x, float *y, float alpha, float beta, cudaStream_t stream) {
+    // matrices with >= 3/16 of their elements stored: one byte per element, x in registers (spmv_dense.cu)
+    const int drc = run_spmv_dense(mat, x, y, alpha, beta, stream);
+    if (drc <= 0) return drc;
     {
     KernelTimer timer(mat, stream);
     switch (mat->spmv_lanes) {

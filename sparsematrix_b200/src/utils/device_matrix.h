@@ -132,6 +132,12 @@ struct sblas_b200_matrix {
     bool csr_sorted = true;             // columns ascending inside every row (required by the tile build)
     TileFormat tile[2];
 
+    // Dense code matrix of W (src/sparse/spmv_dense.cu), built on the first m = 1 product of a matrix
+    // with >= 3/16 of its elements stored: n x dense_kpad one-byte codes, >= T where there is no entry.
+    uint8_t *d_dense_code = nullptr;
+    int64_t dense_kpad = 0;
+    int dense_state = 0;                // 0 = not built yet, 1 = built, -1 = not possible (memory)
+
     // sblas_b200_profile_begin/_end: event pairs around the dominant kernel
     bool profiling = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t> > prof_events;
@@ -152,6 +158,8 @@ int build_tile_format(sblas_b200_matrix *mat, int rows_per_group, cudaStream_t s
 // src/sparse/spmm_tile.cu
 int run_spmm_tile(sblas_b200_matrix *mat, const float *d_a, int m, int lda, float *d_c, int ldc, float alpha,
                   float beta, cudaStream_t stream);
+// src/sparse/spmv_dense.cu: 0 = done, 1 = not applicable (use the row kernels), < 0 = error
+int run_spmv_dense(sblas_b200_matrix *mat, const float *x, float *y, float alpha, float beta, cudaStream_t stream);
 // src/sparse/product.cu
 int product_on_stream(sblas_b200_matrix *mat, const float *d_a, int32_t m, int32_t lda, float *d_c, int32_t ldc,
                       float alpha, float beta, cudaStream_t stream);

@@ -517,15 +517,56 @@ def test_long_row_spmv_full_warp_per_row():
     assert dev.info().spmv_lanes == 32
     a = gen.dense_uniform((1, k), 1); c0 = gen.dense_uniform((1, n), 2); c0[0, 3] = -0.0
     for alpha, beta in ((1.0, 1.0), (1.3, 2.0), (0.7, 0.0)):
-        got = dev.addmatmat_host(a, 1, k, c0.copy(), n, alpha, beta)
+        # (30 % of the elements are stored: without the switch this matrix takes the dense-code kernel)
+        got = _with_env("SBLAS_B200_SPMV_DENSE", "0", lambda: dev.addmatmat_host(a, 1, k, c0.copy(), n, alpha, beta))
         y64, bound = O.addmatmat_f64(s, a, 1, k, c0, n, alpha, beta)
         back = O.error_measures(got, 1, n, n, y64, bound)[0]
         want = O.addmatmat(s, a, 1, k, c0.copy(), n, alpha, beta)
         assert back <= TOL, (alpha, beta, back)
         assert got.reshape(-1)[3].tobytes() == want.reshape(-1)[3].tobytes()       # empty row: exactly beta*c (keeps -0)
-        got2 = dev.addmatmat_host(a, 1, k, c0.copy(), n, alpha, beta)
+        got2 = _with_env("SBLAS_B200_SPMV_DENSE", "0", lambda: dev.addmatmat_host(a, 1, k, c0.copy(), n, alpha, beta))
         assert_bits_equal(got, got2, "run-to-run determinism")
     assert dev.info().device_bytes > 0
+
+
+@pytest.mark.parametrize("n,k,dens", [(333, 5000, 0.30), (1000, 700, 0.5), (515, 1025, 0.25), (64, 16384, 0.2),
+                                      (3000, 512, 0.9), (5, 40, 0.6), (2000, 3000, 0.01)])
+def test_dense_code_spmv(n, k, dens):
+    """m = 1 on matrices with >= 3/16 of their elements stored (spmv_dense.cu): one byte per element, x in
+    registers.  Values against fp64, rows without entries, every column of a row, an Inf / NaN in x where a
+    row has no entry (must not reach that row) and where it has one (must), determinism, and the row kernels
+    on the same handle as a cross-check.  The last case is too sparse for the rule and is forced."""
+    codes = gen.codes_bernoulli(n, k, dens, seed=71)
+    codes[min(3, n - 1), :] = 255                              # empty row
+    if n > 6:
+        codes[6, :] = (np.arange(k) % 250).astype(np.uint8)    # every column stored
+    codes[:, k // 2] = 255                                     # a column no entry uses ...
+    codes[0, k // 2] = 9                                       # ... except row 0
+    tab = gen.codebook()
+    s = O.copyform(codes, n, k, k, tab, 255, True)
+    dev = upload(s)
+    force = "1" if dens < 0.19 else ""
+    a = gen.dense_uniform((1, k), 1); c0 = gen.dense_uniform((1, n), 2); c0[0, min(3, n - 1)] = -0.0
+    bytes_before = dev.info().device_bytes
+    for alpha, beta in ((1.0, 1.0), (1.3, 2.0), (0.7, 0.0)):
+        got = _with_env("SBLAS_B200_SPMV_DENSE", force, lambda: dev.addmatmat_host(a, 1, k, c0.copy(), n, alpha, beta))
+        y64, bound = O.addmatmat_f64(s, a, 1, k, c0, n, alpha, beta)
+        back = O.error_measures(got, 1, n, n, y64, bound)[0]
+        assert back <= TOL, (alpha, beta, back)
+        want = O.addmatmat(s, a, 1, k, c0.copy(), n, alpha, beta)
+        e = min(3, n - 1)
+        assert got.reshape(-1)[e].tobytes() == want.reshape(-1)[e].tobytes()       # empty row: exactly beta*c (keeps -0)
+        again = _with_env("SBLAS_B200_SPMV_DENSE", force, lambda: dev.addmatmat_host(a, 1, k, c0.copy(), n, alpha, beta))
+        assert_bits_equal(got, again, "run-to-run determinism")
+        rows = _with_env("SBLAS_B200_SPMV_DENSE", "0", lambda: dev.addmatmat_host(a, 1, k, c0.copy(), n, alpha, beta))
+        assert O.error_measures(rows, 1, n, n, y64, bound)[0] <= TOL
+        assert np.max(np.abs(rows - got)) <= 2e-5 * max(1.0, float(np.max(np.abs(got))))
+        for bad in (np.inf, np.nan):
+            a_bad = a.copy(); a_bad[0, k // 2] = bad
+            got_bad = _with_env("SBLAS_B200_SPMV_DENSE", force, lambda: dev.addmatmat_host(a_bad, 1, k, c0.copy(), n, alpha, beta))
+            assert not np.isfinite(got_bad.reshape(-1)[0])                          # row 0 uses that column
+            assert_bits_equal(got_bad.reshape(-1)[1:], got.reshape(-1)[1:], f"{bad} in a column only row 0 uses")
+    assert dev.info().device_bytes >= bytes_before + n * k    # the dense code matrix was built and is accounted for
 
 
 def test_spmv_never_touches_x_where_no_entry_is():

@@ -40,12 +40,14 @@ WORKLOADS = {
     "cfg2": ("spmm", 4096, 4096, 0.10, 128, 12),
     "cfg3": ("spmm", 16384, 16384, 0.05, 512, 13),
     "cfg4": ("spmv_powerlaw", 1 << 23, 1 << 23, None, 1, 14),
+    "cfg5": ("spmv", 16384, 16384, 0.50, 1, 100),
 }
 DESCR = {
     "cfg1": "SpMV random 4096x4096 1% density (BASELINE.json configs[0])",
     "cfg2": "pruned-weight SpMM 4096x4096 at 90% sparsity x dense 4096x128 (BASELINE.json configs[1])",
     "cfg3": "SpMM 16384x16384 at 95% sparsity x dense N=512 (BASELINE.json configs[2])",
     "cfg4": "power-law SpMV 2^23 rows ~16 nnz/row, direct CSR (BASELINE.json configs[3])",
+    "cfg5": "density sweep, large end: SpMV 16384x16384 at 50% sparsity (BASELINE.json configs[4])",
 }
 FP32_PEAK_TFLOPS = 2 * 128 * 148 * 1.965e9 / 1e12     # CUDA-core FMA peak at max clock
 
@@ -72,10 +74,18 @@ def build_inputs(workload, rank, scale_rows=1.0):
     return dict(kind=kind, n=n, k=k, m=m, tab=tab, a=a, c=c, codes=codes, nnz=int((codes != 255).sum()))
 
 
+def reads_dense_codes(inp):
+    """The library's own rule (src/sparse/spmv_dense.cu): m = 1, k <= 16384, >= 3/16 of the elements stored."""
+    return inp["m"] == 1 and inp["k"] <= 16384 and 16 * inp["nnz"] >= 3 * inp["n"] * inp["k"]
+
+
 def algorithmic_bytes(inp):
-    """Bytes the dominant kernel must move once: 4 B column + 1 B code per non-zero,
+    """Bytes the dominant kernel must move once, for the device format it actually reads:
+    4 B column + 1 B code per non-zero -- or one code byte per ELEMENT for the dense-code SpMV --,
     row_ptr, X once, C read + written (beta = 1)."""
     n, k, m, nnz = inp["n"], inp["k"], inp["m"], inp["nnz"]
+    if reads_dense_codes(inp):
+        return n * ((k + 511) // 512 * 512) + 4 * (n + 1) + 4 * k * m + 8 * n * m
     return 5 * nnz + 4 * (n + 1) + 4 * k * m + 8 * n * m
 
 
@@ -385,10 +395,15 @@ def run_ours(args):
                 "l2": "flushed before every timed step (256 MiB write); per-step CUDA events summed",
                 "sharding": "row slabs of W, X replicated, no data-path collective" if world > 1 else "single GPU",
                 "device_format": ("quad-row tiles of W (4 fp32 weights + 4 u8 X-row offsets per slot, 5 B/nnz + padding), X chunks staged by TMA"
-                                  if m >= 17 else "CSR(W=S^T) int32 col + u8 code, 5 B/nnz"), "spmv_lanes": info.spmv_lanes,
+                                  if m >= 17 else ("dense code matrix of W, 1 B per element (>= 3/16 of the elements are stored), x in registers"
+                                                   if reads_dense_codes(inp) else "CSR(W=S^T) int32 col + u8 code, 5 B/nnz")),
+                "spmv_lanes": info.spmv_lanes,
                 "long_rows": info.long_rows}),
             "effective_gbs": world * bytes_alg / (ms_step * 1e-3) / 1e9,
-            "warm_l2": {"ms_per_step": warm_ms / args.steps, "value": world * flops / (warm_ms / args.steps * 1e-3) / 1e9},
+            # back-to-back steps without the flush; for working sets beyond the 126 MB L2 (cfg3-5) this is the
+            # "inputs larger than L2" protocol, and hbm_frac is the whole step's algorithmic bytes over the HBM peak
+            "warm_l2": {"ms_per_step": warm_ms / args.steps, "value": world * flops / (warm_ms / args.steps * 1e-3) / 1e9,
+                        "hbm_frac": bytes_alg / (warm_ms / args.steps * 1e-3) / 1e9 / hbm_peak},
             "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
                          "traffic": None, "peak_source": peak_src, "kernel_us": kern_us,
                          "algorithmic_bytes": bytes_alg, "algorithmic_flops": flops,
@@ -409,6 +424,11 @@ def run_ours(args):
             line["roofline"]["onchip"] = {"limiter": "shared-memory pipe (one 128 B wavefront per clock per SM)",
                                           "x_wavefronts": int(wavefronts), "t_floor_us": t_smem_us,
                                           "frac": t_smem_us / kern_us, "fp32_frac_ceiling": 0.25}
+        elif reads_dense_codes(inp):
+            lookups = n * ((k + 511) // 512 * 512) / 32.0 + bytes_alg / 128.0       # one LDS wavefront per 32 codebook look-ups + the loads' data
+            line["roofline"]["onchip"] = {"limiter": "L1/shared data pipe: one conflict-free codebook look-up per element (ncu: l1tex data pipe 81 % busy)",
+                                          "wavefronts": int(lookups), "t_floor_us": lookups / (148 * sm_hz) * 1e6,
+                                          "frac": lookups / (148 * sm_hz) * 1e6 / kern_us}
         else:
             line["roofline"]["onchip"] = {"limiter": "L2 sector requests of the x gathers (one 32 B sector per non-zero; ncu: lts/l1tex throughput)",
                                           "l2_to_sm_bytes": int(32 * nnz + bytes_alg - 4 * k * m),

@@ -640,6 +640,26 @@ static int host_product_overlapped(sblas_b200_matrix *mat, const float *a, int m
     return SBLAS_B200_OK;
 }
 
+// ---- host entry point, small SpMV with mapped caller buffers: no DMA at all ------------------
+// A 16 KB copy costs 4-15 us of copy-engine latency each way, more than the product itself.  For
+// m = 1 and small operands one kernel reads x through the mapped pointer (coalesced) into the
+// handle's staging buffer and the SpMV kernel then updates the caller's y in place through the
+// mapped pointer: two launches on one stream and one synchronisation.
+__global__ void __launch_bounds__(256)
+stage_in_kernel(const float *__restrict__ src, float *__restrict__ dst, int count) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i < count) dst[i] = src[i];
+}
+
+static int host_product_direct(sblas_b200_matrix *mat, const float *a_mapped, float *c_mapped, float alpha, float beta) {
+    SB_LAUNCH(stage_in_kernel, (mat->k + 255) / 256, 256, 0, mat->stream, a_mapped, mat->d_host_a, mat->k);
+    SB_CHECK_LAUNCH();
+    const int rc = product_on_stream(mat, mat->d_host_a, 1, mat->k, c_mapped, mat->n, alpha, beta, mat->stream);
+    if (rc != SBLAS_B200_OK) { cudaStreamSynchronize(mat->stream); return rc; }
+    SB_CUDA(cudaStreamSynchronize(mat->stream));
+    return SBLAS_B200_OK;
+}
+
 }  // namespace sblas_b200
 
 using namespace sblas_b200;
@@ -705,6 +725,11 @@ int sblas_b200_addmatmat_host(sblas_b200_matrix *mat, const float *a, int32_t m,
     rc = ensure_buffer(&mat->d_host_c, &mat->host_c_bytes, (size_t)m * n * 4);
     if (rc != SBLAS_B200_OK) return rc;
     float *c_mapped = need_a ? mapped_pointer(c) : nullptr;
+    if (c_mapped && m == 1 && (size_t)(k + n) * 4 <= ((size_t)256 << 10)) {
+        static const bool direct = [] { const char *e = getenv("SBLAS_B200_HOST_DIRECT"); return !(e && *e == '0'); }();   // A/B switch
+        const float *a_mapped = direct ? mapped_pointer(a) : nullptr;
+        if (a_mapped) return host_product_direct(mat, a_mapped, c_mapped, alpha, beta);
+    }
     if (c_mapped) return host_product_overlapped(mat, a, m, lda, c, c_mapped, ldc, alpha, beta);
     // pageable caller memory (or scale only): copies and kernels back to back on one stream
     if (need_a)

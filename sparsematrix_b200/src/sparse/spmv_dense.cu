@@ -77,7 +77,7 @@ __device__ __forceinline__ float row_block(const uint4 cw, const float (&x)[16],
 template <bool CLEAN>
 __device__ __forceinline__ void walk_rows(const uint8_t *__restrict__ base, int64_t kpad, int row0, int row1, int g0,
                                           int gstep, const float (&xr)[16], uint32_t lane_addr,
-                                          int T, float *part, int colwarps, int cwarp, int lane, int pf_groups) {
+                                          int T, float *part, int part_rows, int cwarp, int lane, int pf_groups) {
     const int64_t stride = kpad * kRowsPerGroup * gstep;
     // lanes 0..15 ask L2 for the four 128-byte lines of the four rows `pf_groups` groups ahead: the loads that
     // follow find them there, so HBM latency is covered by L2 instead of by registers
@@ -110,7 +110,7 @@ __device__ __forceinline__ void walk_rows(const uint8_t *__restrict__ base, int6
         v += __shfl_xor_sync(0xffffffffu, v, 2);
         v += __shfl_xor_sync(0xffffffffu, v, 1);
         const int j = lane >> 3;
-        if ((lane & 7) == 0 && r + j < row1) part[(size_t)(r + j - row0) * colwarps + cwarp] = v;
+        if ((lane & 7) == 0 && r + j < row1) part[(size_t)cwarp * part_rows + (r + j - row0)] = v;   // [warp][row]: the four lanes hit four banks
     }
 }
 
@@ -124,7 +124,7 @@ spmv_dense_kernel(const uint8_t *__restrict__ dense, int64_t kpad, const int32_t
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(smem_raw);
     const uint32_t tab_addr = (sbase + 65535u) & ~65535u;
     float *tab = reinterpret_cast<float *>(smem_raw + (tab_addr - sbase));
-    float *part = tab + 256 * 64;                                       // [rows_per_cta][colwarps]
+    float *part = tab + 256 * 64;                                       // [colwarps][rows_per_cta]
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int cwarp = warp % colwarps, rsplit = warp / colwarps, nsplit = (blockDim.x >> 5) / colwarps;
     const int row0 = blockIdx.x * rows_per_cta;
@@ -158,8 +158,8 @@ spmv_dense_kernel(const uint8_t *__restrict__ dense, int64_t kpad, const int32_t
         tab[(i >> 5) * 64 + (i & 31)] = ((i >> 5) < T) ? table[i >> 5] * alpha : 0.0f;
     __syncthreads();
     const uint32_t lane_addr = tab_addr + lane * 4;
-    if (clean) walk_rows<true>(dense + c0, kpad, row0, row1, rsplit, nsplit, xr, lane_addr, T, part, colwarps, cwarp, lane, pf_groups);
-    else walk_rows<false>(dense + c0, kpad, row0, row1, rsplit, nsplit, xr, lane_addr, T, part, colwarps, cwarp, lane, pf_groups);
+    if (clean) walk_rows<true>(dense + c0, kpad, row0, row1, rsplit, nsplit, xr, lane_addr, T, part, rows_per_cta, cwarp, lane, pf_groups);
+    else walk_rows<false>(dense + c0, kpad, row0, row1, rsplit, nsplit, xr, lane_addr, T, part, rows_per_cta, cwarp, lane, pf_groups);
     __syncthreads();
     for (int t = threadIdx.x; t < row1 - row0; t += blockDim.x) {
         const int len = s_len[t];
@@ -167,7 +167,7 @@ spmv_dense_kernel(const uint8_t *__restrict__ dense, int64_t kpad, const int32_t
         float c = s_c[t];
         if (beta != 1.0f) c *= beta;
         float sum = 0.0f;
-        for (int w = 0; w < colwarps; ++w) sum += part[(size_t)t * colwarps + w];
+        for (int w = 0; w < colwarps; ++w) sum += part[(size_t)w * rows_per_cta + t];
         y[row0 + t] = len ? c + sum : c;
     }
 }

@@ -310,6 +310,13 @@ def test_host_alloc_buffers_take_the_overlapped_route_with_the_same_bits():
     ha[...] = a; hc[...] = c0
     S.AddMatMat(ha, m, k, hc, n, 1.3, 0.7)
     assert_bits_equal(hc, want, "sblas_b200_host_alloc buffers vs pageable")
+    # m = 1 with small operands: x staged by a kernel through the mapped pointer, y updated in place (no DMA)
+    for alpha, beta in ((1.0, 1.0), (1.3, 0.7), (0.0, 2.0)):
+        want1 = S.AddMatMat(a[:1].copy(), 1, k, c0[:1].copy(), n, alpha, beta)
+        hx = sb.host_buffer((1, k)); hy = sb.host_buffer((1, n))
+        hx[...] = a[:1]; hy[...] = c0[:1]
+        S.AddMatMat(hx, 1, k, hy, n, alpha, beta)
+        assert_bits_equal(hy, want1, f"direct small SpMV route alpha={alpha} beta={beta}")
     hc2 = sb.host_buffer((m, n + 8))                                    # ldc > n: the padding stays untouched
     hc2[...] = 7.0; hc2[:, :n] = c0
     S.AddMatMat(ha, m, k, hc2, n + 8, 1.3, 0.7)

@@ -672,6 +672,36 @@ def test_config4_full_size_sampled_rows():
     assert_bits_equal(again, got, "run-to-run determinism at full size")
 
 
+def test_config5_full_size_dense_spmv_sampled_rows_and_row_kernel():
+    # BASELINE.json configs[4], large end of the sweep: 16384 x 16384 at 50 % sparsity, m = 1 (dense-code kernel)
+    n = k = 16384
+    codes = gen.codes_bernoulli(n, k, 0.50, seed=100)
+    tab = gen.codebook()
+    S = sb.SparseMatrix(codes, n, k, k, tab, 255, 1)
+    dev = S.device_matrix()
+    assert dev.nnz == int((codes != 255).sum())
+    a = gen.dense_uniform((1, k), 2); c0 = gen.dense_uniform((1, n), 3)
+    before = dev.info().device_bytes
+    got = dev.addmatmat_host(a, 1, k, c0.copy(), n, 1.3, 2.0)
+    assert dev.info().device_bytes >= before + n * k           # the dense code matrix was built: that kernel ran
+    rows = np.random.default_rng(7).choice(n, 64, replace=False)
+    err = _sampled_backward_error(got[:, rows], codes[rows], tab, a, c0[:, rows], 1.3, 2.0)
+    assert err <= TOL, err
+    again = dev.addmatmat_host(a, 1, k, c0.copy(), n, 1.3, 2.0)
+    assert_bits_equal(again, got, "run-to-run determinism at full size")
+    # the CSR row kernels on the same handle agree to rounding (another summation order, same contract)
+    rows_k = _with_env("SBLAS_B200_SPMV_DENSE", "0", lambda: dev.addmatmat_host(a, 1, k, c0.copy(), n, 1.3, 2.0))
+    assert _sampled_backward_error(rows_k[:, rows], codes[rows], tab, a, c0[:, rows], 1.3, 2.0) <= TOL
+    assert np.max(np.abs(rows_k - got)) <= 1e-5 * float(np.max(np.abs(got))) * 16
+    # linearity in x: W (x1 + x2) = W x1 + W x2 up to rounding (beta = 0 is not "overwrite": C = 0 going in)
+    a2 = gen.dense_uniform((1, k), 9)
+    z = np.zeros((1, n), np.float32)
+    y1 = dev.addmatmat_host(a, 1, k, z.copy(), n, 1.0, 1.0); y2 = dev.addmatmat_host(a2, 1, k, z.copy(), n, 1.0, 1.0)
+    y12 = dev.addmatmat_host(a + a2, 1, k, z.copy(), n, 1.0, 1.0)
+    scale = float(np.abs(a).sum() + np.abs(a2).sum()) / k * 64.0          # ~ sum |w||x| of one row
+    assert np.max(np.abs(y12 - (y1 + y2))) <= 1e-5 * scale * 64
+
+
 def test_products_of_one_handle_on_two_streams_are_ordered_by_the_library():
     """The Xt staging buffer belongs to the handle; products enqueued on different streams must be
     ordered by the library (event), not race on it."""

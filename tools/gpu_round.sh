@@ -9,7 +9,7 @@ nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $O
 python -m pytest tests -m gpu -x -q > $OUT/pytest_gpu.log 2>&1; echo "pytest exit $?" | tee -a $OUT/pytest_gpu.log
 python -c "import __graft_entry__ as g; g.smoke()" > $OUT/smoke.log 2>&1; echo "smoke exit $?" | tee -a $OUT/smoke.log
 (cd sparsematrix_b200 && ./bin/sparse-matrix_test && ./bin/parity_test) > $OUT/cxx_harness.log 2>&1; echo "cxx exit $?" | tee -a $OUT/cxx_harness.log
-for w in cfg2 cfg1 cfg3 cfg4; do
+for w in cfg2 cfg1 cfg3 cfg4 cfg5; do
   python bench.py --workload $w > $OUT/bench_$w.json 2> $OUT/bench_$w.err; echo "bench $w exit $?"
 done
 python bench.py --impl reference --steps 5 --warmup 3 > $OUT/bench_ref_cfg2.json 2> $OUT/bench_ref_cfg2.err

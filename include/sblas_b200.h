@@ -181,6 +181,27 @@ SBLAS_B200_API int sblas_b200_addmatmat_host(sblas_b200_matrix *mat, const float
 SBLAS_B200_API int sblas_b200_addmatmat_dev(sblas_b200_matrix *mat, const float *d_a, int32_t m, int32_t lda,
                                             float *d_c, int32_t ldc, float alpha, float beta, void *stream);
 
+/* ---- the reference's free kernel functions (src/sparse/kernel.h:42-62) ------ */
+/*
+ * For callers that use the reference's free functions directly.  Host pointers,
+ * synchronous, on the current device; sparsematrix_b200/src/sparse/kernel.{h,cc}
+ * bind the reference's own template names to them.
+ *   _scale_host         : c[m x n, ldc] *= beta                 (sblas_beta_operation_kernel, kernel.cc:10-29)
+ *   _transpose_host     : sa[j*ldsa + i] = a[i*lda + j], i < m, j < n; nothing else of sa is written
+ *                                                               (sblas_trans_kernel, kernel.cc:31-187)
+ *   _panel_product_host : C += alpha * A * P for ONE panel P (k x n, n <= 256) given as its byte streams
+ *                         ppos/pval of pos_len entries.  trans == 0: a is m x k, c is m x n, row-major
+ *                         (sblas_kernel_operation, _naive, kernel.cc:213-369); trans != 0: a is k x lda and
+ *                         c is n x ldc with the m values contiguous (sblas_kernel_operation_trans, _trans_ex,
+ *                         kernel.cc:612-800, the layout AddMatMat hands them, sparse-matrix.cc:181-189).
+ *                         Uploads the panel for the call: a convenience, not the fast path.
+ */
+SBLAS_B200_API int sblas_b200_scale_host(float *c, int32_t m, int32_t n, int32_t ldc, float beta);
+SBLAS_B200_API int sblas_b200_transpose_host(const float *a, int32_t m, int32_t n, int32_t lda, float *sa, int32_t ldsa);
+SBLAS_B200_API int sblas_b200_panel_product_host(int32_t trans, int32_t m, int32_t n, int32_t k, const float *a, int32_t lda,
+                                                 float *c, int32_t ldc, float alpha, const uint8_t *ppos, const uint8_t *pval,
+                                                 int32_t pos_len, const float *val_table, int32_t valid_table_size);
+
 /*
  * Page-locked, device-mapped host memory for the caller's a and c.  Any host
  * pointer works with sblas_b200_addmatmat_host(); with memory of this kind

@@ -51,6 +51,9 @@ SYMBOLS = {
     "sblas_b200_copyform_begin": (C.c_int, [_vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp, _vp, _vp]),
     "sblas_b200_copyform_finish": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "sblas_b200_copyform_abort": (None, [_vp]),
+    "sblas_b200_scale_host": (C.c_int, [_vp, _i32, _i32, _i32, _f32]),
+    "sblas_b200_transpose_host": (C.c_int, [_vp, _i32, _i32, _i32, _vp, _i32]),
+    "sblas_b200_panel_product_host": (C.c_int, [_i32, _i32, _i32, _i32, _vp, _i32, _vp, _i32, _f32, _vp, _vp, _i32, _vp, _i32]),
     "sblas_b200_host_alloc": (C.c_int, [_i64, _vp]),
     "sblas_b200_host_free": (C.c_int, [_vp]),
     "sblas_b200_peer_alloc": (C.c_int, [_i32, _i64, _vp, _vp]),

@@ -288,6 +288,7 @@ def test_virtual_shards_concatenate_to_unsharded_result(parts):
 
 # ------------------------------------------------------------------ the C++ harness (src/test), same library
 @pytest.mark.parametrize("binary,expect", [("sparse-matrix_test", "SparseMatrix Test success"),
+                                           ("kernel_test", "Kernel Test success"),
                                            ("parity_test", "Parity Test success")])
 def test_cpp_harness_binaries(binary, expect):
     import os
@@ -297,6 +298,51 @@ def test_cpp_harness_binaries(binary, expect):
         pytest.skip(f"{binary} not built")
     out = subprocess.run([path], capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and expect in out.stdout, out.stdout[-2000:] + out.stderr[-500:]
+
+
+# ------------------------------------------------------------------ the reference's free kernel functions (kernel.h:42-62)
+def test_free_kernel_functions_against_the_reference_library():
+    """sblas_trans_kernel / sblas_beta_operation_kernel / the four panel formulations, device backed
+    (sblas_b200_transpose_host, _scale_host, _panel_product_host), against the unmodified reference's own
+    functions on the same inputs: transposes and the scale bit for bit, panel products within the contract."""
+    L = sb.lib()
+    # kernel_test.cc:33-45: 1023 x 511, lda 512, ldsa 1024
+    a = gen.dense_uniform((1024, 512), 9)
+    sa = np.full((511, 1024), -3.0, np.float32)
+    _capi.check(L.sblas_b200_transpose_host(a.ctypes.data_as(C.c_void_p), 1023, 511, 512, sa.ctypes.data_as(C.c_void_p), 1024))
+    want = np.full((511, 1024), -3.0, np.float32); want[:, :1023] = a[:1023, :511].T
+    assert_bits_equal(sa, want, "transpose (untouched padding included)")
+    if O.have_ref():
+        assert_bits_equal(sa[:, :1023], O.ref_trans_kernel(a, 1023, 511, 512, 1024)[:, :1023], "transpose vs reference")
+    c = gen.dense_uniform((37, 320), 10); c_want = c.copy(); c_want[:, :301] *= np.float32(1.7)
+    _capi.check(L.sblas_b200_scale_host(c.ctypes.data_as(C.c_void_p), 37, 301, 320, 1.7))
+    assert_bits_equal(c, c_want, "beta scale")
+    # one panel with fillers (2 % density), every formulation
+    n, k, m, T = 256, 300, 11, 255
+    codes = gen.codes_bernoulli(n, k, 0.02, seed=78)
+    tab = gen.codebook(T, 1)
+    s = O.copyform(codes, n, k, k, tab, T, True)
+    assert s.nblocks == 1 and int((s.code >= T).sum()) > 0
+    am = gen.dense_uniform((m, k), 2); c0 = gen.dense_uniform((m, n), 3)
+    y64, bound = O.addmatmat_f64(s, am, m, k, c0, n, 1.3, 1.0)
+    for trans in (0, 1):
+        if trans:
+            at = np.zeros((k, 16), np.float32); at[:, :m] = am.T
+            ct = np.zeros((n, 16), np.float32); ct[:, :m] = c0.T
+            _capi.check(L.sblas_b200_panel_product_host(1, m, n, k, at.ctypes.data_as(C.c_void_p), 16, ct.ctypes.data_as(C.c_void_p), 16,
+                                                        1.3, s.pos.ctypes.data_as(C.c_void_p), s.code.ctypes.data_as(C.c_void_p),
+                                                        int(s.pos.shape[0]), s.table.ctypes.data_as(C.c_void_p), T))
+            got = np.ascontiguousarray(ct[:, :m].T)
+            assert np.all(ct[:, m:] == 0.0)                     # the padding of aligned_m stays untouched
+        else:
+            got = c0.copy()
+            _capi.check(L.sblas_b200_panel_product_host(0, m, n, k, am.ctypes.data_as(C.c_void_p), k, got.ctypes.data_as(C.c_void_p), n,
+                                                        1.3, s.pos.ctypes.data_as(C.c_void_p), s.code.ctypes.data_as(C.c_void_p),
+                                                        int(s.pos.shape[0]), s.table.ctypes.data_as(C.c_void_p), T))
+        assert O.error_measures(got, m, n, n, y64, bound)[0] <= TOL, trans
+        if O.have_ref():
+            ref = O.ref_panel_kernel(1, m, n, k, am.copy(), k, c0.copy(), n, 1.3, s.pos, s.code, s.table, T)
+            assert np.max(np.abs(ref - got)) <= 1e-5 * float(np.max(np.abs(ref)))
 
 
 # ------------------------------------------------------------------ host entry point, buffers of the library's allocator

@@ -30,6 +30,29 @@ def test_library_exports_every_declared_symbol():
     assert sb.lib().sblas_b200_abi_version() == 1
 
 
+def test_library_exports_the_reference_free_functions_under_their_mangled_names():
+    # kernel.h:42-62 / kernel.cc:802-811 of the reference: six explicit instantiations.  Code compiled against the
+    # reference header must link against this build, so the names are the Itanium manglings of those instantiations.
+    L = C.CDLL(sb.LIB_PATH)
+    for name in ("_Z27sblas_beta_operation_kernelIfEvPT_iiiS0_",
+                 "_Z18sblas_trans_kernelIfEvPT_iiiS1_i",
+                 "_Z22sblas_kernel_operationIhhfLi8EEviiiPT1_iS1_iS0_PT_PT0_iS1_i",
+                 "_Z28sblas_kernel_operation_naiveIhhfLi8EEviiiPT1_iS1_iS0_PT_PT0_iS1_i",
+                 "_Z28sblas_kernel_operation_transIhhfLi8EEviiiPT1_iS1_iS0_PT_PT0_iS1_i",
+                 "_Z31sblas_kernel_operation_trans_exIhhfLi8EEviiiPT1_iS1_iS0_PT_PT0_iS1_i"):
+        assert hasattr(L, name), name
+    # and the class itself, as the reference instantiates it (sparse-matrix.cc:315), in the static archive that
+    # carries the reference's library name (src/sparse/Makefile:9)
+    import shutil
+    import subprocess
+    archive = os.path.join(os.path.dirname(sb.LIB_PATH), "libsparsematrix.a")
+    if shutil.which("nm") and os.path.exists(archive):
+        syms = subprocess.run(["nm", "--defined-only", archive], capture_output=True, text=True).stdout
+        for name in ("_ZN5sblas12SparseMatrixIhhfLi0ELi8EE9AddMatMatEPfiiS2_iff", "_ZN5sblas12SparseMatrixIhhfLi0ELi8EE8CopyFormEPKhiiiPKfiNS_15SBLAS_TRANSPOSEE",
+                     "_ZN5sblas12SparseMatrixIhhfLi0ELi8EE6CopyToEPfiNS_15SBLAS_TRANSPOSEE", "_Z18sblas_trans_kernelIfEvPT_iiiS1_i"):
+            assert name in syms, name
+
+
 def test_product_does_not_reference_oracle():
     # the oracle is test infrastructure: nothing under sparsematrix_b200/ may import or link it
     for dirpath, _, files in os.walk(os.path.join(ROOT, "sparsematrix_b200")):

@@ -272,6 +272,8 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    step_stats = []                                     # per-step times (ms) of the last timed pass
+
     def timed_pass(steps, profile=False):
         """K steps, L2 flushed before each, one event pair per step on the launching stream."""
         evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
@@ -284,7 +286,10 @@ def run_ours(args):
             step_dev()
             b_ev.record(stream)
         barrier()
-        ms = sum(a_ev.elapsed_time(b_ev) for a_ev, b_ev in evs)
+        per_step = [a_ev.elapsed_time(b_ev) for a_ev, b_ev in evs]
+        ms = sum(per_step)
+        step_stats.clear()
+        step_stats.extend(per_step)
         if profile:
             k_ms, k_cnt = mat.profile_end()
             return ms, k_ms, k_cnt
@@ -299,6 +304,8 @@ def run_ours(args):
     with ClockSampler(local_rank) as clocks:
         total_ms = timed_pass(args.steps)
     launches = L.sblas_b200_launch_count() - launches0
+    steps_sorted = sorted(step_stats)
+    step_median_ms, step_min_ms = steps_sorted[len(steps_sorted) // 2], steps_sorted[0]
     # warm (L2-resident) variant, reported beside the cold number
     barrier()
     w0, w1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -389,7 +396,8 @@ def run_ours(args):
         t_roof_us = max(bytes_alg / (hbm_peak * 1e9), flops / (FP32_PEAK_TFLOPS * 1e12)) * 1e6
         line = {
             "metric": METRIC, "value": value, "unit": "GFLOP/s", "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "ms_per_step_median": step_median_ms,
+            "ms_per_step_min": step_min_ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": config_of(args, inp, {
                 "l2": "flushed before every timed step (256 MiB write); per-step CUDA events summed",

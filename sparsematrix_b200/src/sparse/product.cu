@@ -29,6 +29,11 @@ __device__ __forceinline__ uint32_t ld_stream_u32(const uint32_t *p) { return __
 // x gather: through L1 (ld.global.nc) or L2-only (ld.global.cg); chosen per launch (uniform)
 __device__ __forceinline__ float ld_x(const float *p, int cg) { return cg ? __ldcg(p) : __ldg(p); }
 
+// C in a peer GPU's memory (sblas_b200_peer_open) and beta == 1: the sum is added by a reduction at the owner's memory
+// (one rounding, like the add it replaces) instead of reading C across the link.  `flags` bit 1 of the SpMV kernels.
+constexpr int kFlagXcg = 1, kFlagRedAdd = 2;
+__device__ __forceinline__ void red_add(float *p, float v) { asm volatile("red.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory"); }
+
 // ---- K-scale: C *= beta (alpha == 0 path; sparse-matrix.cc:149-152) ----------------------
 __global__ void __launch_bounds__(256)
 scale_kernel(float *__restrict__ c, int m, int n, int ldc, float beta) {
@@ -47,8 +52,10 @@ __global__ void __launch_bounds__(256)
 spmv_rows_kernel(const int32_t *__restrict__ row_ptr, const int4 *__restrict__ col4,
                  const uint32_t *__restrict__ code4, const float *__restrict__ table, int T,
                  const float *__restrict__ x, float *__restrict__ y, int n, float alpha, float beta,
-                 int long_threshold, int xcg) {
+                 int long_threshold, int flags) {
     __shared__ float s_tab[256];
+    const int xcg = flags & kFlagXcg;
+    const bool red = (flags & kFlagRedAdd) && beta == 1.0f;
     const int sub = threadIdx.x & (LPR - 1);
     const int row = (int)(((size_t)blockIdx.x * 256 + threadIdx.x) / LPR);
     int s = 0, e = 0;
@@ -59,7 +66,7 @@ spmv_rows_kernel(const int32_t *__restrict__ row_ptr, const int4 *__restrict__ c
     const bool mine = row < n && len <= long_threshold;
     // the value this row updates is asked for now, so that its round trip overlaps the walk
     float c0 = 0.0f;
-    if (mine && sub == 0 && !(len == 0 && beta == 1.0f)) c0 = y[row];
+    if (mine && sub == 0 && !(len == 0 && beta == 1.0f) && !red) c0 = y[row];
     float acc = 0.0f;
     if (mine && len > 0) {
         const int b1 = (e - 1) >> 2;
@@ -85,6 +92,7 @@ spmv_rows_kernel(const int32_t *__restrict__ row_ptr, const int4 *__restrict__ c
     for (int o = LPR >> 1; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     if (mine && sub == 0) {
         if (len == 0 && beta == 1.0f) return;           // column without entries, no scale: untouched
+        if (red) { red_add(y + row, acc); return; }
         if (beta != 1.0f) c0 *= beta;
         y[row] = len ? c0 + acc : c0;                   // no entry: exactly the scaled value (keeps -0)
     }
@@ -98,8 +106,10 @@ __global__ void __launch_bounds__(256)
 spmv_sorted_kernel(const int32_t *__restrict__ blk_ptr, const int32_t *__restrict__ slen,
                    const int32_t *__restrict__ order, const int4 *__restrict__ col4,
                    const uint32_t *__restrict__ code4, const float *__restrict__ table, int T,
-                   const float *__restrict__ x, float *__restrict__ y, int n_ordered, float alpha, float beta, int xcg) {
+                   const float *__restrict__ x, float *__restrict__ y, int n_ordered, float alpha, float beta, int flags) {
     __shared__ float s_tab[256];
+    const int xcg = flags & kFlagXcg;
+    const bool red = (flags & kFlagRedAdd) && beta == 1.0f;
     const int sub = threadIdx.x & (LPR - 1);
     const int i = (int)(((size_t)blockIdx.x * 256 + threadIdx.x) / LPR);
     int b0 = 0, len = 0, row = 0;
@@ -107,7 +117,7 @@ spmv_sorted_kernel(const int32_t *__restrict__ blk_ptr, const int32_t *__restric
     s_tab[threadIdx.x] = (threadIdx.x < T) ? table[threadIdx.x] * alpha : 0.0f;    // val_table[code]*alpha
     __syncthreads();
     float c0 = 0.0f;                                        // asked for now: the round trip overlaps the walk
-    if (i < n_ordered && sub == 0 && !(len == 0 && beta == 1.0f)) c0 = y[row];
+    if (i < n_ordered && sub == 0 && !(len == 0 && beta == 1.0f) && !red) c0 = y[row];
     float acc = 0.0f;
     const int nfull = len >> 2, tail = len & 3;
     for (int b = sub; b < nfull; b += LPR) {
@@ -130,6 +140,7 @@ spmv_sorted_kernel(const int32_t *__restrict__ blk_ptr, const int32_t *__restric
     for (int o = LPR >> 1; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     if (i < n_ordered && sub == 0) {
         if (len == 0 && beta == 1.0f) return;               // column without entries, no scale: untouched
+        if (red) { red_add(y + row, acc); return; }
         if (beta != 1.0f) c0 *= beta;
         y[row] = len ? c0 + acc : c0;                       // no entry: exactly the scaled value (keeps -0)
     }
@@ -172,12 +183,13 @@ spmv_long_segment_kernel(const int32_t *__restrict__ seg_begin, const int32_t *_
 // ... and one thread per long row adds its segment sums in segment order (deterministic).
 __global__ void __launch_bounds__(128)
 spmv_long_finish_kernel(const int32_t *__restrict__ long_rows, const int32_t *__restrict__ long_seg_ptr,
-                        const float *__restrict__ partial, float *__restrict__ y, float beta, int n_long) {
+                        const float *__restrict__ partial, float *__restrict__ y, float beta, int n_long, int flags) {
     const int i = blockIdx.x * 128 + threadIdx.x;
     if (i >= n_long) return;
     float t = 0.0f;
     for (int s = long_seg_ptr[i]; s < long_seg_ptr[i + 1]; ++s) t += partial[s];
     const int row = long_rows[i];
+    if ((flags & kFlagRedAdd) && beta == 1.0f) { red_add(y + row, t); return; }
     float c0 = y[row];
     if (beta != 1.0f) c0 *= beta;
     y[row] = c0 + t;
@@ -326,35 +338,36 @@ static int x_load_mode(const sblas_b200_matrix *mat) {
 }
 
 template <int LPR>
-static void launch_spmv_rows(const sblas_b200_matrix *mat, const float *x, float *y, float alpha, float beta,
+static void launch_spmv_rows(const sblas_b200_matrix *mat, const float *x, float *y, float alpha, float beta, int flags,
                              cudaStream_t stream) {
     if (mat->d_row_order) {                                 // skewed row lengths: the sorted copy
         const size_t threads = (size_t)mat->n_ordered * LPR;
         SB_LAUNCH(spmv_sorted_kernel<LPR>, (unsigned)((threads + 255) / 256), 256, 0, stream, mat->d_sblk_ptr, mat->d_slen,
                   mat->d_row_order, mat->d_scol, mat->d_scode, mat->d_table, mat->T, x, y, mat->n_ordered, alpha, beta,
-                  x_load_mode(mat));
+                  flags);
         return;
     }
     const size_t threads = (size_t)mat->n * LPR;
     const unsigned grid = (unsigned)((threads + 255) / 256);
     SB_LAUNCH(spmv_rows_kernel<LPR>, grid, 256, 0, stream, mat->d_row_ptr, reinterpret_cast<const int4 *>(mat->d_col),
               reinterpret_cast<const uint32_t *>(mat->d_code), mat->d_table, mat->T, x, y, mat->n, alpha, beta,
-              mat->long_threshold, x_load_mode(mat));
+              mat->long_threshold, flags);
 }
 
 static int run_spmv(sblas_b200_matrix *mat, const float *x, float *y, float alpha, float beta, cudaStream_t stream) {
     // matrices with >= 3/16 of their elements stored: one byte per element, x in registers (spmv_dense.cu)
     const int drc = run_spmv_dense(mat, x, y, alpha, beta, stream);
     if (drc <= 0) return drc;
+    const int flags = (x_load_mode(mat) ? kFlagXcg : 0) | (is_peer_pointer(y) ? kFlagRedAdd : 0);
     {
     KernelTimer timer(mat, stream);
     switch (mat->spmv_lanes) {
-    case 1: launch_spmv_rows<1>(mat, x, y, alpha, beta, stream); break;
-    case 2: launch_spmv_rows<2>(mat, x, y, alpha, beta, stream); break;
-    case 4: launch_spmv_rows<4>(mat, x, y, alpha, beta, stream); break;
-    case 8: launch_spmv_rows<8>(mat, x, y, alpha, beta, stream); break;
-    case 16: launch_spmv_rows<16>(mat, x, y, alpha, beta, stream); break;
-    default: launch_spmv_rows<32>(mat, x, y, alpha, beta, stream); break;
+    case 1: launch_spmv_rows<1>(mat, x, y, alpha, beta, flags, stream); break;
+    case 2: launch_spmv_rows<2>(mat, x, y, alpha, beta, flags, stream); break;
+    case 4: launch_spmv_rows<4>(mat, x, y, alpha, beta, flags, stream); break;
+    case 8: launch_spmv_rows<8>(mat, x, y, alpha, beta, flags, stream); break;
+    case 16: launch_spmv_rows<16>(mat, x, y, alpha, beta, flags, stream); break;
+    default: launch_spmv_rows<32>(mat, x, y, alpha, beta, flags, stream); break;
     }
     }
     SB_CHECK_LAUNCH();
@@ -365,7 +378,7 @@ static int run_spmv(sblas_b200_matrix *mat, const float *x, float *y, float alph
                   reinterpret_cast<const int4 *>(mat->d_col), reinterpret_cast<const uint32_t *>(mat->d_code),
                   mat->d_table, mat->T, x, alpha, mat->d_partial, x_load_mode(mat));
         SB_LAUNCH(spmv_long_finish_kernel, (mat->n_long + 127) / 128, 128, 0, stream, mat->d_long_rows,
-                  mat->d_long_seg_ptr, mat->d_partial, y, beta, mat->n_long);
+                  mat->d_long_seg_ptr, mat->d_partial, y, beta, mat->n_long, flags);
         SB_CHECK_LAUNCH();
     }
     return SBLAS_B200_OK;

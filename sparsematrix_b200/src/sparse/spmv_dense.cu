@@ -117,7 +117,7 @@ __device__ __forceinline__ void walk_rows(const uint8_t *__restrict__ base, int6
 __global__ void __launch_bounds__(1024, 1)
 spmv_dense_kernel(const uint8_t *__restrict__ dense, int64_t kpad, const int32_t *__restrict__ row_ptr,
                   const float *__restrict__ table, int T, const float *__restrict__ x, float *__restrict__ y, int n, int k,
-                  float alpha, float beta, int rows_per_cta, int colwarps, int pf_groups) {
+                  float alpha, float beta, int rows_per_cta, int colwarps, int pf_groups, int red_add) {
     extern __shared__ __align__(256) unsigned char smem_raw[];
     // the table (256 entries x 256 bytes, 32 lanes x 4 B of each used) on the next 64 KiB boundary of the
     // shared window, the per-(row, warp) sums behind it
@@ -150,9 +150,10 @@ spmv_dense_kernel(const uint8_t *__restrict__ dense, int64_t kpad, const int32_t
     // nothing is left to fetch when the sums are ready
     float *s_c = part + (size_t)rows_per_cta * colwarps;
     int *s_len = reinterpret_cast<int *>(s_c + rows_per_cta);
+    const bool red = red_add && beta == 1.0f;              // y in a peer GPU's memory: sums added by reductions there, y never read
     for (int t = threadIdx.x; t < row1 - row0; t += blockDim.x) {
         s_len[t] = row_ptr[row0 + t + 1] - row_ptr[row0 + t];
-        s_c[t] = y[row0 + t];
+        s_c[t] = red ? 0.0f : y[row0 + t];
     }
     for (int i = threadIdx.x; i < 256 * 32; i += blockDim.x)
         tab[(i >> 5) * 64 + (i & 31)] = ((i >> 5) < T) ? table[i >> 5] * alpha : 0.0f;
@@ -168,6 +169,7 @@ spmv_dense_kernel(const uint8_t *__restrict__ dense, int64_t kpad, const int32_t
         if (beta != 1.0f) c *= beta;
         float sum = 0.0f;
         for (int w = 0; w < colwarps; ++w) sum += part[(size_t)w * rows_per_cta + t];
+        if (red) { if (len) asm volatile("red.global.add.f32 [%0], %1;" ::"l"(y + row0 + t), "f"(sum) : "memory"); continue; }
         y[row0 + t] = len ? c + sum : c;
     }
 }
@@ -240,7 +242,7 @@ int run_spmv_dense(sblas_b200_matrix *mat, const float *x, float *y, float alpha
         ~Timer() { if (a) { cudaEventRecord(b, st); mat->prof_events.push_back(std::make_pair(a, b)); } }
     } timer(mat, stream);
     SB_LAUNCH(spmv_dense_kernel, grid, colwarps * rowsplit * 32, smem, stream, mat->d_dense_code, mat->dense_kpad, mat->d_row_ptr,
-              mat->d_table, mat->T, x, y, mat->n, mat->k, alpha, beta, rows_per_cta, colwarps, pf_groups);
+              mat->d_table, mat->T, x, y, mat->n, mat->k, alpha, beta, rows_per_cta, colwarps, pf_groups, is_peer_pointer(y) ? 1 : 0);
     SB_CHECK_LAUNCH();
     return SBLAS_B200_OK;
 }

@@ -30,8 +30,8 @@ __device__ __forceinline__ uint32_t ld_stream_u32(const uint32_t *p) { return __
 __device__ __forceinline__ float ld_x(const float *p, int cg) { return cg ? __ldcg(p) : __ldg(p); }
 
 // C in a peer GPU's memory (sblas_b200_peer_open) and beta == 1: the sum is added by a reduction at the owner's memory
-// (one rounding, like the add it replaces) instead of reading C across the link.  `flags` bit 1 of the SpMV kernels.
-constexpr int kFlagXcg = 1, kFlagRedAdd = 2;
+// (one rounding, like the add it replaces) instead of reading C across the link: the RED instances of the SpMV
+// kernels (a run-time flag in the one kernel cost the local case 2.4 % on the power-law matrix).
 __device__ __forceinline__ void red_add(float *p, float v) { asm volatile("red.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory"); }
 
 // ---- K-scale: C *= beta (alpha == 0 path; sparse-matrix.cc:149-152) ----------------------
@@ -47,15 +47,13 @@ scale_kernel(float *__restrict__ c, int m, int n, int ldc, float beta) {
 // (128-bit) and four codes (32-bit) per iteration and gathers four x values; partial
 // sums are combined with __shfl_xor.  Rows longer than long_threshold are left to the
 // split-row kernels below.
-template <int LPR>
+template <int LPR, bool RED>
 __global__ void __launch_bounds__(256)
 spmv_rows_kernel(const int32_t *__restrict__ row_ptr, const int4 *__restrict__ col4,
                  const uint32_t *__restrict__ code4, const float *__restrict__ table, int T,
                  const float *__restrict__ x, float *__restrict__ y, int n, float alpha, float beta,
-                 int long_threshold, int flags) {
+                 int long_threshold, int xcg) {
     __shared__ float s_tab[256];
-    const int xcg = flags & kFlagXcg;
-    const bool red = (flags & kFlagRedAdd) && beta == 1.0f;
     const int sub = threadIdx.x & (LPR - 1);
     const int row = (int)(((size_t)blockIdx.x * 256 + threadIdx.x) / LPR);
     int s = 0, e = 0;
@@ -66,7 +64,7 @@ spmv_rows_kernel(const int32_t *__restrict__ row_ptr, const int4 *__restrict__ c
     const bool mine = row < n && len <= long_threshold;
     // the value this row updates is asked for now, so that its round trip overlaps the walk
     float c0 = 0.0f;
-    if (mine && sub == 0 && !(len == 0 && beta == 1.0f) && !red) c0 = y[row];
+    if (!RED && mine && sub == 0 && !(len == 0 && beta == 1.0f)) c0 = y[row];
     float acc = 0.0f;
     if (mine && len > 0) {
         const int b1 = (e - 1) >> 2;
@@ -92,7 +90,7 @@ spmv_rows_kernel(const int32_t *__restrict__ row_ptr, const int4 *__restrict__ c
     for (int o = LPR >> 1; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     if (mine && sub == 0) {
         if (len == 0 && beta == 1.0f) return;           // column without entries, no scale: untouched
-        if (red) { red_add(y + row, acc); return; }
+        if (RED) { red_add(y + row, acc); return; }          // beta == 1 (run_spmv)
         if (beta != 1.0f) c0 *= beta;
         y[row] = len ? c0 + acc : c0;                   // no entry: exactly the scaled value (keeps -0)
     }
@@ -101,15 +99,13 @@ spmv_rows_kernel(const int32_t *__restrict__ row_ptr, const int4 *__restrict__ c
 // Same, on the length-sorted copy of the short rows (skewed matrices): position i of the sorted
 // order starts on a block boundary, so only a row's last block needs masking, and the rows of one
 // warp are about equally long.  y is addressed through the order list.
-template <int LPR>
+template <int LPR, bool RED>
 __global__ void __launch_bounds__(256)
 spmv_sorted_kernel(const int32_t *__restrict__ blk_ptr, const int32_t *__restrict__ slen,
                    const int32_t *__restrict__ order, const int4 *__restrict__ col4,
                    const uint32_t *__restrict__ code4, const float *__restrict__ table, int T,
-                   const float *__restrict__ x, float *__restrict__ y, int n_ordered, float alpha, float beta, int flags) {
+                   const float *__restrict__ x, float *__restrict__ y, int n_ordered, float alpha, float beta, int xcg) {
     __shared__ float s_tab[256];
-    const int xcg = flags & kFlagXcg;
-    const bool red = (flags & kFlagRedAdd) && beta == 1.0f;
     const int sub = threadIdx.x & (LPR - 1);
     const int i = (int)(((size_t)blockIdx.x * 256 + threadIdx.x) / LPR);
     int b0 = 0, len = 0, row = 0;
@@ -117,7 +113,7 @@ spmv_sorted_kernel(const int32_t *__restrict__ blk_ptr, const int32_t *__restric
     s_tab[threadIdx.x] = (threadIdx.x < T) ? table[threadIdx.x] * alpha : 0.0f;    // val_table[code]*alpha
     __syncthreads();
     float c0 = 0.0f;                                        // asked for now: the round trip overlaps the walk
-    if (i < n_ordered && sub == 0 && !(len == 0 && beta == 1.0f) && !red) c0 = y[row];
+    if (!RED && i < n_ordered && sub == 0 && !(len == 0 && beta == 1.0f)) c0 = y[row];
     float acc = 0.0f;
     const int nfull = len >> 2, tail = len & 3;
     for (int b = sub; b < nfull; b += LPR) {
@@ -140,7 +136,7 @@ spmv_sorted_kernel(const int32_t *__restrict__ blk_ptr, const int32_t *__restric
     for (int o = LPR >> 1; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     if (i < n_ordered && sub == 0) {
         if (len == 0 && beta == 1.0f) return;               // column without entries, no scale: untouched
-        if (red) { red_add(y + row, acc); return; }
+        if (RED) { red_add(y + row, acc); return; }          // beta == 1 (run_spmv)
         if (beta != 1.0f) c0 *= beta;
         y[row] = len ? c0 + acc : c0;                       // no entry: exactly the scaled value (keeps -0)
     }
@@ -183,13 +179,13 @@ spmv_long_segment_kernel(const int32_t *__restrict__ seg_begin, const int32_t *_
 // ... and one thread per long row adds its segment sums in segment order (deterministic).
 __global__ void __launch_bounds__(128)
 spmv_long_finish_kernel(const int32_t *__restrict__ long_rows, const int32_t *__restrict__ long_seg_ptr,
-                        const float *__restrict__ partial, float *__restrict__ y, float beta, int n_long, int flags) {
+                        const float *__restrict__ partial, float *__restrict__ y, float beta, int n_long, int red) {
     const int i = blockIdx.x * 128 + threadIdx.x;
     if (i >= n_long) return;
     float t = 0.0f;
     for (int s = long_seg_ptr[i]; s < long_seg_ptr[i + 1]; ++s) t += partial[s];
     const int row = long_rows[i];
-    if ((flags & kFlagRedAdd) && beta == 1.0f) { red_add(y + row, t); return; }
+    if (red) { red_add(y + row, t); return; }               // beta == 1 (run_spmv)
     float c0 = y[row];
     if (beta != 1.0f) c0 *= beta;
     y[row] = c0 + t;
@@ -337,38 +333,44 @@ static int x_load_mode(const sblas_b200_matrix *mat) {
     return mat->k > 32768 ? 1 : 0;
 }
 
-template <int LPR>
-static void launch_spmv_rows(const sblas_b200_matrix *mat, const float *x, float *y, float alpha, float beta, int flags,
+template <int LPR, bool RED>
+static void launch_spmv_rows(const sblas_b200_matrix *mat, const float *x, float *y, float alpha, float beta, int xcg,
                              cudaStream_t stream) {
     if (mat->d_row_order) {                                 // skewed row lengths: the sorted copy
         const size_t threads = (size_t)mat->n_ordered * LPR;
-        SB_LAUNCH(spmv_sorted_kernel<LPR>, (unsigned)((threads + 255) / 256), 256, 0, stream, mat->d_sblk_ptr, mat->d_slen,
+        SB_LAUNCH((spmv_sorted_kernel<LPR, RED>), (unsigned)((threads + 255) / 256), 256, 0, stream, mat->d_sblk_ptr, mat->d_slen,
                   mat->d_row_order, mat->d_scol, mat->d_scode, mat->d_table, mat->T, x, y, mat->n_ordered, alpha, beta,
-                  flags);
+                  xcg);
         return;
     }
     const size_t threads = (size_t)mat->n * LPR;
     const unsigned grid = (unsigned)((threads + 255) / 256);
-    SB_LAUNCH(spmv_rows_kernel<LPR>, grid, 256, 0, stream, mat->d_row_ptr, reinterpret_cast<const int4 *>(mat->d_col),
+    SB_LAUNCH((spmv_rows_kernel<LPR, RED>), grid, 256, 0, stream, mat->d_row_ptr, reinterpret_cast<const int4 *>(mat->d_col),
               reinterpret_cast<const uint32_t *>(mat->d_code), mat->d_table, mat->T, x, y, mat->n, alpha, beta,
-              mat->long_threshold, flags);
+              mat->long_threshold, xcg);
 }
 
 static int run_spmv(sblas_b200_matrix *mat, const float *x, float *y, float alpha, float beta, cudaStream_t stream) {
     // matrices with >= 3/16 of their elements stored: one byte per element, x in registers (spmv_dense.cu)
     const int drc = run_spmv_dense(mat, x, y, alpha, beta, stream);
     if (drc <= 0) return drc;
-    const int flags = (x_load_mode(mat) ? kFlagXcg : 0) | (is_peer_pointer(y) ? kFlagRedAdd : 0);
+    const int xcg = x_load_mode(mat);
+    const bool red = beta == 1.0f && is_peer_pointer(y);    // y across NVLink: add at the owner, do not read it
     {
     KernelTimer timer(mat, stream);
+#define SB_SPMV_CASE(L) \
+    case L: red ? launch_spmv_rows<L, true>(mat, x, y, alpha, beta, xcg, stream) \
+                : launch_spmv_rows<L, false>(mat, x, y, alpha, beta, xcg, stream); break
     switch (mat->spmv_lanes) {
-    case 1: launch_spmv_rows<1>(mat, x, y, alpha, beta, flags, stream); break;
-    case 2: launch_spmv_rows<2>(mat, x, y, alpha, beta, flags, stream); break;
-    case 4: launch_spmv_rows<4>(mat, x, y, alpha, beta, flags, stream); break;
-    case 8: launch_spmv_rows<8>(mat, x, y, alpha, beta, flags, stream); break;
-    case 16: launch_spmv_rows<16>(mat, x, y, alpha, beta, flags, stream); break;
-    default: launch_spmv_rows<32>(mat, x, y, alpha, beta, flags, stream); break;
+    SB_SPMV_CASE(1);
+    SB_SPMV_CASE(2);
+    SB_SPMV_CASE(4);
+    SB_SPMV_CASE(8);
+    SB_SPMV_CASE(16);
+    default: red ? launch_spmv_rows<32, true>(mat, x, y, alpha, beta, xcg, stream)
+                 : launch_spmv_rows<32, false>(mat, x, y, alpha, beta, xcg, stream); break;
     }
+#undef SB_SPMV_CASE
     }
     SB_CHECK_LAUNCH();
     if (mat->n_long) {
@@ -376,9 +378,9 @@ static int run_spmv(sblas_b200_matrix *mat, const float *x, float *y, float alph
         if (rc != SBLAS_B200_OK) return rc;
         SB_LAUNCH(spmv_long_segment_kernel, mat->n_long_seg, 256, 0, stream, mat->d_seg_begin, mat->d_seg_end,
                   reinterpret_cast<const int4 *>(mat->d_col), reinterpret_cast<const uint32_t *>(mat->d_code),
-                  mat->d_table, mat->T, x, alpha, mat->d_partial, x_load_mode(mat));
+                  mat->d_table, mat->T, x, alpha, mat->d_partial, xcg);
         SB_LAUNCH(spmv_long_finish_kernel, (mat->n_long + 127) / 128, 128, 0, stream, mat->d_long_rows,
-                  mat->d_long_seg_ptr, mat->d_partial, y, beta, mat->n_long, flags);
+                  mat->d_long_seg_ptr, mat->d_partial, y, beta, mat->n_long, red ? 1 : 0);
         SB_CHECK_LAUNCH();
     }
     return SBLAS_B200_OK;

@@ -2,7 +2,8 @@
 into rank 0's memory through an NVLink-mapped pointer (sharding.PeerOutput), and the assembled C
 must equal, bit for bit, the all-gather of the slabs computed into local memory -- the kernels
 are the same, only the C pointer differs (for beta == 1 the SpMM tile kernel adds into peer memory
-with red.global.add.f32 instead of a read-modify-write: same single rounding, cases m = 64 and 8).
+with red.global.add.f32 instead of a read-modify-write: same single rounding, cases m = 64 and 8; the
+SpMV kernels likewise, m = 1 here and on a skewed CSR matrix with split long rows).
 Skipped on a box with one GPU."""
 import os
 import socket
@@ -67,6 +68,37 @@ def _worker(rank, world, port, ret):
             ref = (c0[:, 512:768] * beta if beta != 1.0 else c0[:, 512:768]).cpu().numpy().view(np.uint32)
             results.append(bool(np.array_equal(got.reshape(m, n)[:, 512:768], ref)))
         out.close()
+
+    # A skewed CSR matrix (the length-sorted SpMV copy and the split long rows), rows halved by hand: with
+    # beta == 1 the remote rank's row sums arrive as reductions (the RED instances of the SpMV kernels).
+    n2 = k2 = 1 << 16
+    row_ptr, col, code = gen.powerlaw_csr(n2, k2, seed=14, x_min=8, cap=1 << 15)
+    half = n2 // 2 + 77
+    r0, r1 = (half, n2) if rank == 0 else (0, half)      # the 12436-entry row is in the remote rank's part
+    e0, e1 = int(row_ptr[r0]), int(row_ptr[r1])
+    part = sb.DeviceMatrix.upload_csr((row_ptr[r0:r1 + 1] - e0).astype(np.int32), col[e0:e1], code[e0:e1],
+                                      gen.codebook(), 255, r1 - r0, k2, device=rank)
+    inf = part.info()
+    a = torch.from_numpy(gen.dense_uniform((1, k2), 3)).to(dev)
+    c0 = torch.from_numpy(gen.dense_uniform((1, n2), 4)).to(dev)
+    for alpha, beta in ((1.0, 1.0), (0.7, 1.0), (1.3, 2.0)):
+        c_local = c0[:, r0:r1].clone()
+        part.addmatmat_dev(a, 1, k2, c_local, r1 - r0, alpha, beta)
+        pieces = [torch.empty((1, n2 - half), device=dev), torch.empty((1, half), device=dev)]
+        dist.all_gather(pieces, c_local)
+        full_gather = torch.cat([pieces[1], pieces[0]], dim=1)
+        out = sharding.PeerOutput(1, n2, root=0, device=rank)
+        if rank == 0:
+            out.tensor().copy_(c0)
+        out.finish()
+        out.write_slab(part, a, k2, r0, alpha, beta)
+        out.finish()
+        if rank == 0:
+            results.append(bool(np.array_equal(out.tensor().cpu().numpy().view(np.uint32),
+                                               full_gather.cpu().numpy().view(np.uint32))))
+        out.close()
+    if rank == 1:
+        ret["skewed"] = (int(inf.long_rows), int(inf.max_row_nnz))
     if rank == 0:
         ret["ok"] = results
         ret["splits"] = [int(x) for x in splits]
@@ -92,3 +124,4 @@ def test_peer_mapped_output_equals_allgather_of_local_slabs():
             assert p.exitcode == 0, f"worker exit code {p.exitcode}"
         assert ret["ok"] and all(ret["ok"]), dict(ret)
         assert ret["splits"][0] == 0 and ret["splits"][-1] == 2348
+        assert ret["skewed"][0] > 0 and ret["skewed"][1] > 8192, dict(ret)     # the remote part had split rows

@@ -229,6 +229,11 @@ SBLAS_B200_API int sblas_b200_host_free(void *ptr);
  *                 (same single rounding; subnormal sums are flushed to zero there)
  *   _peer_close : unmap a pointer of _peer_open
  *   _peer_free  : free a pointer of _peer_alloc (after every peer has closed it)
+ *   _peer_register / _peer_unregister : declare a range of peer memory the application
+ *                 mapped by other means (one process driving several GPUs with
+ *                 cudaDeviceEnablePeerAccess, cuMemMap of a fabric handle, a symmetric
+ *                 heap), so that products into it take the same epilogues.  Nothing is
+ *                 mapped or freed; ranges must not overlap.  No device is needed.
  * The owner must not read C before the writers' streams have been synchronised
  * (an application-level barrier); stores to peer memory are not ordered with
  * the owner's own stream.
@@ -238,6 +243,8 @@ SBLAS_B200_API int sblas_b200_peer_alloc(int32_t device, int64_t bytes, void **d
 SBLAS_B200_API int sblas_b200_peer_open(int32_t device, const uint8_t *handle, int64_t bytes, void **d_ptr);
 SBLAS_B200_API int sblas_b200_peer_close(void *d_ptr);
 SBLAS_B200_API int sblas_b200_peer_free(void *d_ptr);
+SBLAS_B200_API int sblas_b200_peer_register(void *d_ptr, int64_t bytes);
+SBLAS_B200_API int sblas_b200_peer_unregister(void *d_ptr);
 
 /* ---- kernel timing (bench.py's roofline leg) ------------------------------ */
 /*

@@ -60,6 +60,8 @@ SYMBOLS = {
     "sblas_b200_peer_open": (C.c_int, [_i32, _vp, _i64, _vp]),
     "sblas_b200_peer_close": (C.c_int, [_vp]),
     "sblas_b200_peer_free": (C.c_int, [_vp]),
+    "sblas_b200_peer_register": (C.c_int, [_vp, _i64]),
+    "sblas_b200_peer_unregister": (C.c_int, [_vp]),
     # sblas_b200_host.h
     "sblas_host_create": (_vp, []),
     "sblas_host_free": (None, [_vp]),

@@ -19,8 +19,8 @@ namespace sblas_b200 {
 namespace {
 std::mutex g_peer_lock;
 std::map<void *, int> g_peer_owned;    // pointer -> device, allocations of sblas_b200_peer_alloc
-struct Mapping { size_t bytes; int device; };
-std::map<uintptr_t, Mapping> g_peer_opened;   // base -> extent, mappings of sblas_b200_peer_open
+struct Mapping { size_t bytes; int device; };   // device < 0: a range of sblas_b200_peer_register (not ours to unmap)
+std::map<uintptr_t, Mapping> g_peer_opened;   // base -> extent, mappings of sblas_b200_peer_open / _peer_register
 std::atomic<int> g_peer_open_count{0};
 }  // namespace
 
@@ -89,7 +89,8 @@ int sblas_b200_peer_close(void *d_ptr) {
     {
         std::lock_guard<std::mutex> guard(g_peer_lock);
         auto it = g_peer_opened.find(reinterpret_cast<uintptr_t>(d_ptr));
-        if (it == g_peer_opened.end()) return fail(SBLAS_B200_EINVAL, "peer_close: not a pointer of sblas_b200_peer_open");
+        if (it == g_peer_opened.end() || it->second.device < 0)
+            return fail(SBLAS_B200_EINVAL, "peer_close: not a pointer of sblas_b200_peer_open");
         device = it->second.device;
         g_peer_opened.erase(it);
         g_peer_open_count.fetch_sub(1, std::memory_order_relaxed);
@@ -97,6 +98,36 @@ int sblas_b200_peer_close(void *d_ptr) {
     DeviceScope scope(device);
     if (!scope.ok()) return SBLAS_B200_ECUDA;
     SB_CUDA(cudaIpcCloseMemHandle(d_ptr));
+    return SBLAS_B200_OK;
+}
+
+// Ranges of peer memory the application mapped itself (one process driving several GPUs with
+// cudaDeviceEnablePeerAccess, cuMemMap of a fabric handle, a symmetric heap): the same epilogues apply.
+int sblas_b200_peer_register(void *d_ptr, int64_t bytes) {
+    if (!d_ptr) return fail(SBLAS_B200_EINVAL, "peer_register: null pointer");
+    if (bytes <= 0) return fail(SBLAS_B200_EINVAL, "peer_register: bytes = %lld", (long long)bytes);
+    const uintptr_t a = reinterpret_cast<uintptr_t>(d_ptr);
+    std::lock_guard<std::mutex> guard(g_peer_lock);
+    auto next = g_peer_opened.lower_bound(a);                   // first range starting at or after a
+    if (next != g_peer_opened.end() && next->first - a < (uintptr_t)bytes)
+        return fail(SBLAS_B200_EINVAL, "peer_register: overlaps a range already known");
+    if (next != g_peer_opened.begin()) {
+        auto prev = next;
+        --prev;
+        if (a - prev->first < prev->second.bytes) return fail(SBLAS_B200_EINVAL, "peer_register: overlaps a range already known");
+    }
+    g_peer_opened[a] = Mapping{(size_t)bytes, -1};
+    g_peer_open_count.fetch_add(1, std::memory_order_relaxed);
+    return SBLAS_B200_OK;
+}
+
+int sblas_b200_peer_unregister(void *d_ptr) {
+    std::lock_guard<std::mutex> guard(g_peer_lock);
+    auto it = g_peer_opened.find(reinterpret_cast<uintptr_t>(d_ptr));
+    if (it == g_peer_opened.end() || it->second.device >= 0)
+        return fail(SBLAS_B200_EINVAL, "peer_unregister: not a pointer of sblas_b200_peer_register");
+    g_peer_opened.erase(it);
+    g_peer_open_count.fetch_sub(1, std::memory_order_relaxed);
     return SBLAS_B200_OK;
 }
 

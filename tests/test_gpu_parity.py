@@ -251,6 +251,44 @@ def test_device_pointer_entry_matches_host_entry():
     assert_bits_equal(d_c.cpu().numpy(), want, "dev vs host entry point")
 
 
+def test_output_in_registered_peer_range_gives_the_same_bits():
+    """sblas_b200_peer_register: C declared to lie in peer memory takes the epilogues for NVLink-mapped output
+    (no L2 prefetch of C; for beta == 1 the sums are added by red.global.add.f32, C never read) -- every SpMV
+    kernel and the SpMM tile kernel, against the same product into an undeclared buffer.  On one GPU the "peer"
+    range is local memory, which the reductions serve just the same (two GPUs: tests/test_peer_output_gpu.py)."""
+    import torch
+    L = sb.lib()
+    tab = gen.codebook()
+    mats = []
+    codes = gen.codes_bernoulli(3000, 1500, 0.06, seed=21)
+    codes[256:512] = 255                                                     # an empty panel
+    mats.append(("rows", sb.SparseMatrix(codes, 3000, 1500, 1500, tab, 255, 1).device_matrix(), 3000, 1500))
+    n, k = 1 << 16, 1 << 16
+    row_ptr, col, code = gen.powerlaw_csr(n, k, seed=14, x_min=8, cap=1 << 15)
+    skew = sb.DeviceMatrix.upload_csr(row_ptr, col, code, tab, 255, n, k)
+    assert skew.info().long_rows > 0
+    mats.append(("sorted+long", skew, n, k))
+    codes = gen.codes_bernoulli(1100, 2048, 0.5, seed=22)
+    mats.append(("dense codes", sb.SparseMatrix(codes, 1100, 2048, 2048, tab, 255, 1).device_matrix(), 1100, 2048))
+    for name, dev, n, k in mats:
+        for m in (1, 8, 64):
+            if name == "sorted+long" and m == 64:
+                continue
+            a = torch.from_numpy(gen.dense_uniform((m, k), 31 + m)).cuda()
+            c0 = torch.from_numpy(gen.dense_uniform((m, n), 32 + m)).cuda()
+            for alpha, beta in ((1.0, 1.0), (0.7, 1.0), (1.3, 2.0)):
+                want = c0.clone()
+                dev.addmatmat_dev(a, m, k, want, n, alpha, beta)
+                got = c0.clone()
+                assert L.sblas_b200_peer_register(C.c_void_p(got.data_ptr()), got.numel() * 4) == _capi.OK
+                try:
+                    dev.addmatmat_dev(a, m, k, got, n, alpha, beta)
+                    torch.cuda.synchronize()
+                finally:
+                    assert L.sblas_b200_peer_unregister(C.c_void_p(got.data_ptr())) == _capi.OK
+                assert_bits_equal(got.cpu().numpy(), want.cpu().numpy(), f"{name} m={m} alpha={alpha} beta={beta}")
+
+
 @pytest.mark.parametrize("parts", [2, 3, 8])
 def test_virtual_shards_concatenate_to_unsharded_result(parts):
     # SURVEY.md 8(e): run the slabs one after another on one device; every output row is computed

@@ -137,6 +137,20 @@ def test_argument_errors_are_reported_without_a_device():
     assert L.sblas_b200_peer_alloc(0, 64, None, handle) == _capi.EINVAL
     assert L.sblas_b200_peer_close(C.c_void_p(1234)) == _capi.EINVAL
     assert L.sblas_b200_peer_free(C.c_void_p(1234)) == _capi.EINVAL
+    # ranges the application mapped itself: bookkeeping only, overlaps refused, each call pairs with its own undo
+    base = 0x7000_0000_0000
+    assert L.sblas_b200_peer_register(None, 64) == _capi.EINVAL
+    assert L.sblas_b200_peer_register(C.c_void_p(base), 0) == _capi.EINVAL
+    assert L.sblas_b200_peer_register(C.c_void_p(base), 4096) == _capi.OK
+    assert L.sblas_b200_peer_register(C.c_void_p(base), 4096) == _capi.EINVAL             # the same range again
+    assert L.sblas_b200_peer_register(C.c_void_p(base + 4095), 16) == _capi.EINVAL        # tail overlap
+    assert L.sblas_b200_peer_register(C.c_void_p(base - 8), 16) == _capi.EINVAL           # head overlap
+    assert L.sblas_b200_peer_register(C.c_void_p(base + 4096), 16) == _capi.OK            # adjacent is fine
+    assert L.sblas_b200_peer_close(C.c_void_p(base)) == _capi.EINVAL                      # not a _peer_open mapping
+    assert L.sblas_b200_peer_unregister(C.c_void_p(base + 8)) == _capi.EINVAL             # not a range start
+    assert L.sblas_b200_peer_unregister(C.c_void_p(base)) == _capi.OK
+    assert L.sblas_b200_peer_unregister(C.c_void_p(base)) == _capi.EINVAL
+    assert L.sblas_b200_peer_unregister(C.c_void_p(base + 4096)) == _capi.OK
     import torch
     if not torch.cuda.is_available():
         assert L.sblas_b200_peer_alloc(0, 64, C.byref(out), handle) == _capi.ECUDA

@@ -77,9 +77,10 @@ def host_buffer(shape, dtype=np.float32):
 class DeviceMatrix:
     """W = S^T resident on one GPU (opaque sblas_b200_matrix)."""
 
-    def __init__(self, handle, owned=True):
+    def __init__(self, handle, owned=True, owner=None):
         self._h = C.c_void_p(handle) if not isinstance(handle, C.c_void_p) else handle
         self._owned = owned
+        self._owner = owner                 # a borrowed handle keeps the object that owns it alive
 
     # ---- construction -------------------------------------------------------------------
     @classmethod
@@ -308,11 +309,12 @@ class SparseMatrix:
         _capi.check(self._L.sblas_host_load(self._h, os.fsencode(path)))
 
     def device_matrix(self):
-        """The uploaded matrix of this object on the current CUDA device (borrowed, owned by the object)."""
+        """The uploaded matrix of this object on the current CUDA device (borrowed: owned by this object, which the
+        returned wrapper keeps alive; a later CopyForm / Destroy / load of this object still invalidates it)."""
         h = self._L.sblas_host_device_matrix(self._h)
         if not h:
             raise _capi.SblasError(_capi.ECUDA, self._L.sblas_b200_last_error().decode())
-        return DeviceMatrix(h, owned=False)
+        return DeviceMatrix(h, owned=False, owner=self)
 
     def upload_slab(self, col_begin, col_end, device=0):
         pos, code, table, T, bb, bib = self.members()

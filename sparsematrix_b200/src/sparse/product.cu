@@ -350,10 +350,17 @@ static void launch_spmv_rows(const sblas_b200_matrix *mat, const float *x, float
               mat->long_threshold, xcg);
 }
 
-static int run_spmv(sblas_b200_matrix *mat, const float *x, float *y, float alpha, float beta, cudaStream_t stream) {
+static int run_spmv_sorted_to_peer(sblas_b200_matrix *mat, const float *x, float *y, float alpha, float beta,
+                                   cudaStream_t stream);
+
+static int run_spmv(sblas_b200_matrix *mat, const float *x, float *y, float alpha, float beta, cudaStream_t stream,
+                    bool staged = false) {
     // matrices with >= 3/16 of their elements stored: one byte per element, x in registers (spmv_dense.cu)
-    const int drc = run_spmv_dense(mat, x, y, alpha, beta, stream);
+    const int drc = staged ? 1 : run_spmv_dense(mat, x, y, alpha, beta, stream);
     if (drc <= 0) return drc;
+    // the length-sorted copy visits rows in sorted order: into peer memory its row sums would travel as scattered
+    // 4-byte packets (8 GPUs into one: 3.3 ms instead of 0.6) -- they are formed locally and added out in row order
+    if (!staged && mat->d_row_order && is_peer_pointer(y)) return run_spmv_sorted_to_peer(mat, x, y, alpha, beta, stream);
     const int xcg = x_load_mode(mat);
     const bool red = beta == 1.0f && is_peer_pointer(y);    // y across NVLink: add at the owner, do not read it
     {
@@ -483,8 +490,8 @@ fill_negzero_kernel(float4 *__restrict__ p, size_t n4) {
 
 template <bool VEC>
 __global__ void __launch_bounds__(256)
-combine_out_kernel(const float *__restrict__ c_in, float *__restrict__ p, const int32_t *__restrict__ row_ptr,
-                   float *__restrict__ out, int ldo, int m, int n, float beta) {
+combine_out_kernel(const float *c_in, float *__restrict__ p, const int32_t *__restrict__ row_ptr,
+                   float *out, int ldo, int m, int n, float beta) {       // c_in == out is allowed (in place)
     const float z = __int_as_float(0x80000000);
     if (VEC) {
         const int n4 = n >> 2;
@@ -514,6 +521,73 @@ combine_out_kernel(const float *__restrict__ c_in, float *__restrict__ p, const 
             out[(size_t)i * ldo + j] = cv;
         }
     }
+}
+
+// ---- SpMV of the length-sorted copy with y in a peer GPU's memory -----------------------------
+// out pass for beta == 1: y[j] += p[j] for the rows that have entries, as reductions at the owner's memory -- four rows
+// per reduction where all four have entries (one 512-byte request per warp), single ones otherwise; p goes back to -0.
+__global__ void __launch_bounds__(256)
+add_out_red_kernel(float *__restrict__ p, const int32_t *__restrict__ row_ptr, float *__restrict__ y, int n, int vec) {
+    const float z = __int_as_float(0x80000000);
+    const int n4 = n >> 2;
+    for (int q = blockIdx.x * 256 + threadIdx.x; q < n4; q += gridDim.x * 256) {
+        const int j = q << 2;
+        const float4 pv = *reinterpret_cast<const float4 *>(p + j);
+        *reinterpret_cast<float4 *>(p + j) = make_float4(z, z, z, z);
+        const int r0 = row_ptr[j], r1 = row_ptr[j + 1], r2 = row_ptr[j + 2], r3 = row_ptr[j + 3], r4 = row_ptr[j + 4];
+        if (vec && r1 != r0 && r2 != r1 && r3 != r2 && r4 != r3) {
+            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(y + j), "f"(pv.x), "f"(pv.y), "f"(pv.z),
+                         "f"(pv.w) : "memory");
+        } else {
+            if (r1 != r0) red_add(y + j, pv.x);
+            if (r2 != r1) red_add(y + j + 1, pv.y);
+            if (r3 != r2) red_add(y + j + 2, pv.z);
+            if (r4 != r3) red_add(y + j + 3, pv.w);
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+        const int j = (n4 << 2) + threadIdx.x;
+        const float pv = p[j];
+        p[j] = z;
+        if (row_ptr[j + 1] != row_ptr[j]) red_add(y + j, pv);
+    }
+}
+
+static int run_spmv_sorted_to_peer(sblas_b200_matrix *mat, const float *x, float *y, float alpha, float beta,
+                                   cudaStream_t stream) {
+    const int n = mat->n;
+    const size_t padded = ((size_t)n + 3) & ~(size_t)3;
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    SB_CUDA(cudaStreamIsCapturing(stream, &cap));
+    if (cap != cudaStreamCaptureStatusNone && mat->peer_y_bytes < padded * 4)
+        return fail(SBLAS_B200_EINVAL, "peer output during stream capture: call once outside the capture first");
+    const size_t had = mat->peer_y_bytes;
+    int rc = ensure_buffer(&mat->d_peer_y, &mat->peer_y_bytes, padded * 4);
+    if (rc != SBLAS_B200_OK) return rc;
+    if (mat->peer_y_bytes != had) mat->peer_y_clean = false;
+    if (!mat->peer_y_clean) {
+        const size_t n4 = mat->peer_y_bytes / 16;
+        SB_LAUNCH(fill_negzero_kernel, (unsigned)std::min<size_t>((n4 + 255) / 256, 148 * 8), 256, 0, stream,
+                  reinterpret_cast<float4 *>(mat->d_peer_y), n4);
+        SB_CHECK_LAUNCH();
+    }
+    mat->peer_y_clean = false;                              // until the out pass has put -0 back
+    rc = run_spmv(mat, x, mat->d_peer_y, alpha, 1.0f, stream, true);     // (-0) + sum = sum, bit for bit
+    if (rc != SBLAS_B200_OK) return rc;
+    const bool aligned = (reinterpret_cast<uintptr_t>(y) & 15) == 0;
+    if (beta == 1.0f) {
+        const unsigned grid = (unsigned)std::min<size_t>((padded / 4 + 255) / 256, 148 * 16);
+        SB_LAUNCH(add_out_red_kernel, std::max(1u, grid), 256, 0, stream, mat->d_peer_y, mat->d_row_ptr, y, n, aligned ? 1 : 0);
+    } else {                                               // y read over the link once, in whole rows of the warp
+        const bool vec = (n & 3) == 0 && aligned;
+        const size_t work = vec ? (size_t)n / 4 : (size_t)n;
+        const unsigned grid = (unsigned)std::min<size_t>((work + 255) / 256, 148 * 16);
+        if (vec) SB_LAUNCH(combine_out_kernel<true>, grid, 256, 0, stream, y, mat->d_peer_y, mat->d_row_ptr, y, n, 1, n, beta);
+        else SB_LAUNCH(combine_out_kernel<false>, grid, 256, 0, stream, y, mat->d_peer_y, mat->d_row_ptr, y, n, 1, n, beta);
+    }
+    SB_CHECK_LAUNCH();
+    mat->peer_y_clean = true;
+    return SBLAS_B200_OK;
 }
 
 // A strided copy whose rows touch is one plain copy: a single DMA descriptor instead of one per row.

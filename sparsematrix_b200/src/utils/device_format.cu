@@ -429,7 +429,7 @@ static void release(sblas_b200_matrix *mat) {
     cudaFree(mat->d_long_rows); cudaFree(mat->d_long_seg_ptr); cudaFree(mat->d_seg_begin); cudaFree(mat->d_seg_end);
     for (TileFormat &tf : mat->tile) { cudaFree(tf.d_blocks); cudaFree(tf.d_grp_ptr); cudaFree(tf.d_grp_nq); }
     cudaFree(mat->d_ws); cudaFree(mat->d_partial); cudaFree(mat->d_host_a); cudaFree(mat->d_host_c);
-    cudaFree(mat->d_host_p); cudaFree(mat->d_dense_code);
+    cudaFree(mat->d_host_p); cudaFree(mat->d_dense_code); cudaFree(mat->d_peer_y);
     if (mat->stream) cudaStreamDestroy(mat->stream);
     if (mat->ws_event) cudaEventDestroy(mat->ws_event);
     if (mat->stream2) cudaStreamDestroy(mat->stream2);

@@ -122,6 +122,8 @@ struct sblas_b200_matrix {
     // host path, pinned caller buffers: the product runs into d_host_p (kept at -0.0f between calls)
     // while C travels in on stream2; one kernel then combines both straight into the caller's C
     float *d_host_p = nullptr;  size_t host_p_bytes = 0;   bool host_p_clean = false;
+    // SpMV of the length-sorted copy into peer memory: row sums formed here (kept at -0.0f), added out in row order
+    float *d_peer_y = nullptr;  size_t peer_y_bytes = 0;   bool peer_y_clean = false;
     // and, for large m, in slices of A/C rows so that copies in, products and copies out overlap
     cudaStream_t stream2 = nullptr, stream3 = nullptr;  // copies in / copies out
     std::vector<cudaEvent_t> host_events;                // per slice: A arrived, C arrived, result ready

@@ -263,9 +263,17 @@ def test_output_in_registered_peer_range_gives_the_same_bits():
     codes = gen.codes_bernoulli(3000, 1500, 0.06, seed=21)
     codes[256:512] = 255                                                     # an empty panel
     mats.append(("rows", sb.SparseMatrix(codes, 3000, 1500, 1500, tab, 255, 1).device_matrix(), 3000, 1500))
-    n, k = 1 << 16, 1 << 16
+    # skewed rows, the length-sorted copy forced, split long rows, rows without entries, n not a multiple of 4: its
+    # row sums are formed in a local buffer and added out in row order (run_spmv_sorted_to_peer)
+    n, k = (1 << 16) + 7, 1 << 16
     row_ptr, col, code = gen.powerlaw_csr(n, k, seed=14, x_min=8, cap=1 << 15)
-    skew = sb.DeviceMatrix.upload_csr(row_ptr, col, code, tab, 255, n, k)
+    lens = np.diff(row_ptr).astype(np.int64)
+    keep = np.ones(col.shape[0], bool)
+    keep[row_ptr[10]:row_ptr[17]] = False; keep[row_ptr[n - 2]:row_ptr[n - 1]] = False
+    lens[10:17] = 0; lens[n - 2] = 0
+    col, code = col[keep], code[keep]
+    row_ptr = np.concatenate(([0], np.cumsum(lens))).astype(np.int32)
+    skew = _with_env("SBLAS_B200_SORT_ROWS", "1", lambda: sb.DeviceMatrix.upload_csr(row_ptr, col, code, tab, 255, n, k))
     assert skew.info().long_rows > 0
     mats.append(("sorted+long", skew, n, k))
     codes = gen.codes_bernoulli(1100, 2048, 0.5, seed=22)
@@ -279,14 +287,18 @@ def test_output_in_registered_peer_range_gives_the_same_bits():
             for alpha, beta in ((1.0, 1.0), (0.7, 1.0), (1.3, 2.0)):
                 want = c0.clone()
                 dev.addmatmat_dev(a, m, k, want, n, alpha, beta)
-                got = c0.clone()
-                assert L.sblas_b200_peer_register(C.c_void_p(got.data_ptr()), got.numel() * 4) == _capi.OK
-                try:
-                    dev.addmatmat_dev(a, m, k, got, n, alpha, beta)
-                    torch.cuda.synchronize()
-                finally:
-                    assert L.sblas_b200_peer_unregister(C.c_void_p(got.data_ptr())) == _capi.OK
-                assert_bits_equal(got.cpu().numpy(), want.cpu().numpy(), f"{name} m={m} alpha={alpha} beta={beta}")
+                for shift in ((0, 1) if m == 1 else (0,)):                      # shift 1: y off the 16-byte grid
+                    buf = torch.empty(m * n + shift, device="cuda")
+                    got = buf[shift:].view(m, n)
+                    got.copy_(c0)
+                    assert L.sblas_b200_peer_register(C.c_void_p(buf.data_ptr()), buf.numel() * 4) == _capi.OK
+                    try:
+                        dev.addmatmat_dev(a, m, k, got, n, alpha, beta)
+                        torch.cuda.synchronize()
+                    finally:
+                        assert L.sblas_b200_peer_unregister(C.c_void_p(buf.data_ptr())) == _capi.OK
+                    assert_bits_equal(got.cpu().numpy(), want.cpu().numpy(),
+                                      f"{name} m={m} alpha={alpha} beta={beta} shift={shift}")
 
 
 @pytest.mark.parametrize("parts", [2, 3, 8])

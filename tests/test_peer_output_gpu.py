@@ -69,9 +69,10 @@ def _worker(rank, world, port, ret):
             results.append(bool(np.array_equal(got.reshape(m, n)[:, 512:768], ref)))
         out.close()
 
-    # A skewed CSR matrix (the length-sorted SpMV copy and the split long rows), rows halved by hand: with
-    # beta == 1 the remote rank's row sums arrive as reductions (the RED instances of the SpMV kernels).
-    n2 = k2 = 1 << 16
+    # A skewed CSR matrix (the length-sorted SpMV copy and the split long rows), rows halved by hand: the remote
+    # rank forms its row sums locally and adds them out in row order (reductions for beta == 1, product.cu:
+    # run_spmv_sorted_to_peer); the unsorted row kernels above add theirs by reductions straight from the kernel.
+    n2 = k2 = 1 << 17                                       # >= 65536 rows in the remote part: it gets the sorted copy
     row_ptr, col, code = gen.powerlaw_csr(n2, k2, seed=14, x_min=8, cap=1 << 15)
     half = n2 // 2 + 77
     r0, r1 = (half, n2) if rank == 0 else (0, half)      # the 12436-entry row is in the remote rank's part

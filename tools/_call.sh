@@ -1,5 +1,5 @@
-python -m pytest tests -m gpu -x -q 2>&1 | tail -2
-python bench.py --no-cpu-baseline > gpurun_out/final_cfg2.json 2>gpurun_out/final_cfg2.err; echo "bench exit $?"
-python -c "
-import json; d=json.load(open('gpurun_out/final_cfg2.json')); print('cfg2: step %.1f us e2e %.0f value %.0f launches %s clocks %s' % (d['ms_per_step']*1e3, d['e2e']['value'], d['value'], d['gpu_launches'], d['clocks']))"
-python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -2
+for v in base evl base evl; do
+  LIB=""; [ "$v" != "base" ] && LIB=$PWD/sparsematrix_b200/lib/exp_$v.so
+  SBLAS_B200_LIB=$LIB python bench.py --workload cfg4 --steps 30 --warmup 5 --no-cpu-baseline 2>/dev/null | python -c "
+import json,sys; d=json.load(sys.stdin); print('cfg4 $v: step %.1f us kernel %.1f warm %.1f' % (d['ms_per_step']*1e3, d['roofline']['kernel_us'], d['warm_l2']['ms_per_step']*1e3))"
+done

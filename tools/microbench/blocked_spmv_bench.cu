@@ -43,7 +43,7 @@ __global__ void fill_lrow(uint16_t *lrow, const int *seg_ptr, int nseg, int RB) 
     for (int t = threadIdx.x; t < L; t += blockDim.x) lrow[b + t] = (uint16_t)(((long long)t * RB) / L);
 }
 
-template <int VEC>
+template <int U>
 __global__ void __launch_bounds__(1024, 1)
 pass1_kernel(const uint2 *__restrict__ lcol4, const uint32_t *__restrict__ code4, const float *__restrict__ x,
              const float *__restrict__ table, float alpha, float4 *__restrict__ p4, int chunks_per_cb) {
@@ -55,21 +55,25 @@ pass1_kernel(const uint2 *__restrict__ lcol4, const uint32_t *__restrict__ code4
     if (threadIdx.x < 256) tab_s[threadIdx.x] = table[threadIdx.x] * alpha;
     __syncthreads();
     const size_t q0 = (size_t)blockIdx.x * (CHUNK / 4);
-#pragma unroll 2
-    for (int q = threadIdx.x; q < CHUNK / 4; q += 1024) {
-        const uint2 lc = __ldcs(lcol4 + q0 + q);
-        const uint32_t cd = __ldcs(code4 + q0 + q);
-        float4 p;
-        p.x = x_s[lc.x & 0xffffu] * tab_s[cd & 255u];
-        p.y = x_s[lc.x >> 16] * tab_s[(cd >> 8) & 255u];
-        p.z = x_s[lc.y & 0xffffu] * tab_s[(cd >> 16) & 255u];
-        p.w = x_s[lc.y >> 16] * tab_s[cd >> 24];
-        __stcs(p4 + q0 + q, p);
+    for (int q = threadIdx.x; q < CHUNK / 4; q += 1024 * U) {      // U independent 12-byte loads in flight per thread
+        uint2 lc[U];
+        uint32_t cd[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) { lc[u] = __ldcs(lcol4 + q0 + q + u * 1024); cd[u] = __ldcs(code4 + q0 + q + u * 1024); }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            float4 p;
+            p.x = x_s[lc[u].x & 0xffffu] * tab_s[cd[u] & 255u];
+            p.y = x_s[lc[u].x >> 16] * tab_s[(cd[u] >> 8) & 255u];
+            p.z = x_s[lc[u].y & 0xffffu] * tab_s[(cd[u] >> 16) & 255u];
+            p.w = x_s[lc[u].y >> 16] * tab_s[cd[u] >> 24];
+            __stcs(p4 + q0 + q + u * 1024, p);
+        }
     }
 }
 
-// K = entries per thread and segment held in registers (segments of up to K * 1024 entries)
-template <int K>
+// K = entries per thread and segment held in registers (segments of up to K * 1024 entries); D = segments loaded ahead
+template <int K, int D>
 __global__ void __launch_bounds__(1024, 1)
 pass2_kernel(const uint16_t *__restrict__ lrow, const float *__restrict__ p, const int *__restrict__ seg_ptr,
              float *__restrict__ y, int RB, int n) {
@@ -80,36 +84,41 @@ pass2_kernel(const uint16_t *__restrict__ lrow, const float *__restrict__ p, con
     for (int i = threadIdx.x; i < RB; i += 1024) y_s[i] = 0.0f;
     for (int i = threadIdx.x; i <= NCB; i += 1024) sp[i] = seg_ptr[rb * NCB + i];
     __syncthreads();
-    uint32_t r[K], rprev[K];
-    float v[K];
-    auto load = [&](int s) {
+    uint32_t r[D][K], rprev[D][K];
+    float v[D][K];
+    auto load = [&](int s, uint32_t (&rr)[K], uint32_t (&rp)[K], float (&vv)[K]) {
         const int b = sp[s], e = sp[s + 1];
 #pragma unroll
         for (int q = 0; q < K; ++q) {
             const int i = b + threadIdx.x + q * 1024;
-            r[q] = 0xffffffffu; rprev[q] = 0xfffffffeu; v[q] = 0.0f;
+            rr[q] = 0xffffffffu; rp[q] = 0xfffffffeu; vv[q] = 0.0f;
             if (i < e) {
-                r[q] = lrow[i];
-                v[q] = __ldcs(p + i);
-                if (i > b) rprev[q] = lrow[i - 1];
+                rr[q] = lrow[i];
+                vv[q] = __ldcs(p + i);
+                if (i > b) rp[q] = lrow[i - 1];
             }
         }
     };
-    load(0);
-    for (int s = 0; s < NCB; ++s) {
-        uint32_t cr[K], cp[K];
-        float cv[K];
 #pragma unroll
-        for (int q = 0; q < K; ++q) { cr[q] = r[q]; cp[q] = rprev[q]; cv[q] = v[q]; }
-        if (s + 1 < NCB) load(s + 1);
+    for (int d = 0; d < D; ++d) load(d, r[d], rprev[d], v[d]);
+    for (int s0 = 0; s0 < NCB; s0 += D) {
 #pragma unroll
-        for (int q = 0; q < K; ++q) {
-            if (cr[q] != 0xffffffffu) {
-                if (cr[q] != cp[q]) y_s[cr[q]] += cv[q];                // head of a run (runs have length 1 here)
-                else atomicAdd(&y_s[cr[q]], cv[q]);                      // stand-in for the in-run continuation
+        for (int d = 0; d < D; ++d) {
+            const int s = s0 + d;
+            uint32_t cr[K], cp[K];
+            float cv[K];
+#pragma unroll
+            for (int q = 0; q < K; ++q) { cr[q] = r[d][q]; cp[q] = rprev[d][q]; cv[q] = v[d][q]; }
+            if (s + D < NCB) load(s + D, r[d], rprev[d], v[d]);
+#pragma unroll
+            for (int q = 0; q < K; ++q) {
+                if (cr[q] != 0xffffffffu) {
+                    if (cr[q] != cp[q]) y_s[cr[q]] += cv[q];            // head of a run (runs have length 1 here)
+                    else atomicAdd(&y_s[cr[q]], cv[q]);                  // stand-in for the in-run continuation
+                }
             }
+            __syncthreads();
         }
-        __syncthreads();
     }
     for (int i = threadIdx.x; i < RB; i += 1024) {
         const size_t row = (size_t)rb * RB + i;
@@ -155,9 +164,12 @@ int main() {
     printf("entries %zu, segments %d (max %d entries), RB %d rows, covered %d\n", nnz, nseg, maxlen, RB, sp[nseg] - sp[0]);
 
     const int smem1 = (CB + 256) * 4, smem2 = RB * 4 + (NCB + 1) * 4;
+    CK(cudaFuncSetAttribute(pass1_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem1));
     CK(cudaFuncSetAttribute(pass1_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem1));
-    CK(cudaFuncSetAttribute(pass2_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
-    CK(cudaFuncSetAttribute(pass2_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
+    CK(cudaFuncSetAttribute(pass1_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem1));
+    CK(cudaFuncSetAttribute((pass2_kernel<2, 1>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
+    CK(cudaFuncSetAttribute((pass2_kernel<2, 2>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
+    CK(cudaFuncSetAttribute((pass2_kernel<2, 4>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
     const int items = (int)(nnz / CHUNK);
@@ -177,9 +189,13 @@ int main() {
         CK(cudaGetLastError());
         printf("%-28s mean %8.1f us  min %8.1f us  %7.1f GB/s\n", what, sum / 8 * 1e3, best * 1e3, bytes / (sum / 8 * 1e-3) * 1e-9);
     };
-    time("pass 1 (7 B/entry)", [&] { pass1_kernel<4><<<items, 1024, smem1>>>(lcol4, code4, x, table, 1.0f, (float4 *)p, items / (k / CB)); },
-         (double)nnz * 7 + (double)items * CB * 4);
-    time("pass 2, K = 2 (6 B/entry)", [&] { pass2_kernel<2><<<NRB, 1024, smem2>>>(lrow, p, seg_ptr, y, RB, n); }, (double)nnz * 6);
-    time("pass 2, K = 3 (6 B/entry)", [&] { pass2_kernel<3><<<NRB, 1024, smem2>>>(lrow, p, seg_ptr, y, RB, n); }, (double)nnz * 6);
+    const int cpc = items / (k / CB);
+    const double b1 = (double)nnz * 7 + (double)items * CB * 4;
+    time("pass 1, 2 loads in flight", [&] { pass1_kernel<2><<<items, 1024, smem1>>>(lcol4, code4, x, table, 1.0f, (float4 *)p, cpc); }, b1);
+    time("pass 1, 4 loads in flight", [&] { pass1_kernel<4><<<items, 1024, smem1>>>(lcol4, code4, x, table, 1.0f, (float4 *)p, cpc); }, b1);
+    time("pass 1, 8 loads in flight", [&] { pass1_kernel<8><<<items, 1024, smem1>>>(lcol4, code4, x, table, 1.0f, (float4 *)p, cpc); }, b1);
+    time("pass 2, 1 segment ahead", [&] { pass2_kernel<2, 1><<<NRB, 1024, smem2>>>(lrow, p, seg_ptr, y, RB, n); }, (double)nnz * 6);
+    time("pass 2, 2 segments ahead", [&] { pass2_kernel<2, 2><<<NRB, 1024, smem2>>>(lrow, p, seg_ptr, y, RB, n); }, (double)nnz * 6);
+    time("pass 2, 4 segments ahead", [&] { pass2_kernel<2, 4><<<NRB, 1024, smem2>>>(lrow, p, seg_ptr, y, RB, n); }, (double)nnz * 6);
     return 0;
 }

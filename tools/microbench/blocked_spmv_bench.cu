@@ -139,6 +139,66 @@ pass2_kernel(const uint16_t *__restrict__ lrow, const float *__restrict__ p, con
     }
 }
 
+// pass 1, persistent: G CTAs, CTA c takes the contiguous entry range [c, c + 1) * nnz / G and refills its x tile only where
+// the range crosses into the next column block (every column block holds per_cb entries in the synthetic data).
+template <int U, int CBT, int NT>
+__global__ void __launch_bounds__(NT, 1024 / NT)
+pass1p_kernel(const uint2 *__restrict__ lcol4, const uint32_t *__restrict__ code4, const float *__restrict__ x,
+              const float *__restrict__ table, float alpha, float4 *__restrict__ p4, size_t nq, size_t per_cb_q) {
+    extern __shared__ float smem[];
+    float *x_s = smem, *tab_s = smem + CBT;
+    if (threadIdx.x < 256) tab_s[threadIdx.x] = table[threadIdx.x] * alpha;
+    const size_t step = (size_t)NT * U;
+    size_t q = (nq * blockIdx.x / gridDim.x) / step * step;
+    const size_t q_end = blockIdx.x + 1 == gridDim.x ? nq : (nq * (blockIdx.x + 1) / gridDim.x) / step * step;
+    while (q < q_end) {
+        const size_t cb = q / per_cb_q;
+        const size_t stop = (cb + 1) * per_cb_q < q_end ? (cb + 1) * per_cb_q : q_end;
+        __syncthreads();                                        // everyone is done with the previous tile
+        const float4 *xg = reinterpret_cast<const float4 *>(x + cb * CBT);
+        for (int i = threadIdx.x; i < CBT / 4; i += NT) reinterpret_cast<float4 *>(x_s)[i] = xg[i];
+        __syncthreads();
+        for (size_t qq = q + threadIdx.x; qq < stop; qq += step) {
+            uint2 lc[U];
+            uint32_t cd[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+                if (qq + u * NT < stop) { lc[u] = __ldcs(lcol4 + qq + u * NT); cd[u] = __ldcs(code4 + qq + u * NT); }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (qq + u * NT < stop) {
+                    float4 p;
+                    p.x = x_s[lc[u].x & (CBT - 1)] * tab_s[cd[u] & 255u];
+                    p.y = x_s[(lc[u].x >> 16) & (CBT - 1)] * tab_s[(cd[u] >> 8) & 255u];
+                    p.z = x_s[lc[u].y & (CBT - 1)] * tab_s[(cd[u] >> 16) & 255u];
+                    p.w = x_s[(lc[u].y >> 16) & (CBT - 1)] * tab_s[cd[u] >> 24];
+                    __stcs(p4 + qq + u * NT, p);
+                }
+            }
+        }
+        q = stop;
+    }
+}
+
+template <int U, int CBT, int NT>
+static void run_pass1p(const char *what, int G, const uint2 *lcol4, const uint32_t *code4, const float *x, const float *table,
+                       float *p, size_t nnz, int k, cudaEvent_t e0, cudaEvent_t e1) {
+    const int smem = (CBT + 256) * 4;
+    CK(cudaFuncSetAttribute((pass1p_kernel<U, CBT, NT>), cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    float sum = 0.0f;
+    for (int it = -2; it < 8; ++it) {
+        CK(cudaEventRecord(e0));
+        pass1p_kernel<U, CBT, NT><<<G, NT, smem>>>(lcol4, code4, x, table, 1.0f, (float4 *)p, nnz / 4, nnz / 4 / (k / CBT));
+        CK(cudaEventRecord(e1));
+        CK(cudaEventSynchronize(e1));
+        float ms;
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        if (it >= 0) sum += ms;
+    }
+    CK(cudaGetLastError());
+    printf("pass 1 %-58s %7.1f us\n", what, sum / 8 * 1e3);
+}
+
 // pass 2 with 8 + 16 byte loads: a thread takes four neighbouring entries of the segment (segments start on multiples of
 // four entries); D = segments loaded ahead.  The run-head test looks inside the quad only (enough for the synthetic data).
 template <int D, int NT>
@@ -257,9 +317,11 @@ int main() {
     CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
 
     run_pass1<4, 0, 32768, 1024>("128 KB tile, 1024 threads, 4 loads in flight", lcol4, code4, x, table, p, nnz, k, e0, e1);
-    run_pass1<4, 0, 8192, 256>("32 KB tile, 4 CTAs of 256 threads per SM", lcol4, code4, x, table, p, nnz, k, e0, e1);
-    run_pass1<8, 0, 8192, 256>("  same, 8 loads in flight", lcol4, code4, x, table, p, nnz, k, e0, e1);
-    run_pass1<4, 0, 16384, 256>("64 KB tile, 3 CTAs of 256 threads per SM", lcol4, code4, x, table, p, nnz, k, e0, e1);
+    run_pass1<8, 0, 8192, 256>("32 KB tile, 4 CTAs of 256 threads per SM, 8 loads", lcol4, code4, x, table, p, nnz, k, e0, e1);
+    run_pass1p<4, 32768, 1024>("persistent, 128 KB tile, 148 CTAs of 1024 threads, 4 loads", 148, lcol4, code4, x, table, p, nnz, k, e0, e1);
+    run_pass1p<8, 32768, 1024>("persistent, 128 KB tile, 148 CTAs of 1024 threads, 8 loads", 148, lcol4, code4, x, table, p, nnz, k, e0, e1);
+    run_pass1p<4, 32768, 512>("persistent, 128 KB tile, 148 CTAs of 512 threads, 4 loads", 148, lcol4, code4, x, table, p, nnz, k, e0, e1);
+    run_pass1p<8, 16384, 512>("persistent, 64 KB tile, 296 CTAs of 512 threads, 8 loads", 296, lcol4, code4, x, table, p, nnz, k, e0, e1);
 
     // segments: rb-major, nnz / nseg entries on average, +-12 % pseudo-random
     auto setup_pass2 = [&](int NRB, int cap) {
@@ -287,11 +349,7 @@ int main() {
         return RB;
     };
     int RB = setup_pass2(296, 2048);
-    run_pass2<2, 1, 0, 1024>("113 KB tile, 1024 threads, next segment in registers", lrow, p, seg_ptr, y, 296, RB, n, e0, e1);
-    run_pass2v<1, 1024>("  4 entries per thread (8 + 16 byte loads), next segment", lrow, p, seg_ptr, y, 296, RB, n, e0, e1);
-    run_pass2v<2, 1024>("  4 entries per thread, next 2 segments", lrow, p, seg_ptr, y, 296, RB, n, e0, e1);
-    run_pass2v<4, 1024>("  4 entries per thread, next 4 segments", lrow, p, seg_ptr, y, 296, RB, n, e0, e1);
-    run_pass2v<4, 512>("  4 entries per thread, 512 threads, next 4 segments", lrow, p, seg_ptr, y, 296, RB, n, e0, e1);
-    run_pass2v<8, 512>("  4 entries per thread, 512 threads, next 8 segments", lrow, p, seg_ptr, y, 296, RB, n, e0, e1);
+    run_pass2v<1, 1024>("4 entries per thread (8 + 16 byte loads), 1024 threads, next segment", lrow, p, seg_ptr, y, 296, RB, n, e0, e1);
+    run_pass2v<4, 512>("4 entries per thread, 512 threads, next 4 segments", lrow, p, seg_ptr, y, 296, RB, n, e0, e1);
     return 0;
 }

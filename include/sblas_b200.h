@@ -125,6 +125,15 @@ SBLAS_B200_API int sblas_b200_partition(const int32_t *block_bounds, const int32
                                         int32_t nblocks, int32_t cols, int32_t parts, int32_t *col_splits);
 
 /*
+ * The same for a matrix given as CSR of W (sblas_b200_upload_csr): row_splits[parts+1],
+ * nnz-balanced, interior values multiples of `align` (a power of two; 256 keeps the slabs
+ * panel aligned like the stream form).  Slab g is rows [row_splits[g], row_splits[g+1]):
+ * upload it with row_ptr + row_splits[g] rebased to 0.  Pure host code.
+ */
+SBLAS_B200_API int sblas_b200_partition_csr(const int32_t *row_ptr, int32_t n, int32_t parts, int32_t align,
+                                            int32_t *row_splits);
+
+/*
  * CopyForm on the device (reference src/sparse/sparse-matrix.cc:21-99): dense
  * code matrix -> the reference's byte streams, bit for bit (fillers, per-panel
  * restart of the position, empty panels not recorded), and from them the device
@@ -256,6 +265,26 @@ SBLAS_B200_API int sblas_b200_peer_unregister(void *d_ptr);
  */
 SBLAS_B200_API int sblas_b200_profile_begin(sblas_b200_matrix *mat);
 SBLAS_B200_API int sblas_b200_profile_end(sblas_b200_matrix *mat, double *total_ms, int64_t *launches);
+
+/*
+ * What the most recent product on this handle ran: the name of its dominant
+ * kernel (the one _profile_begin/_end bracket) and the bytes that kernel has to
+ * move once per launch for the device format it reads -- the "algorithmic bytes"
+ * of the roofline: format bytes per stored non-zero, row pointers,
+ * X once, C read and written once.  m is the dense row count of that product.
+ */
+typedef struct sblas_b200_product_info {
+    char kernel[64];
+    int32_t m;
+    int32_t reserved;
+    int64_t algorithmic_bytes;
+    int64_t algorithmic_flops;    /* 2 * nnz * m */
+    double format_bytes_per_nnz;  /* 5 for CSR with codes and the quad-row tiles, 13 for the two-pass blocked SpMV, ... */
+} sblas_b200_product_info;
+SBLAS_B200_API int sblas_b200_last_product(const sblas_b200_matrix *mat, sblas_b200_product_info *out);
+
+/* fp32 FMA throughput of `device` measured with a register-resident FMA loop (TFLOP/s): the roofline's compute peak. */
+SBLAS_B200_API int sblas_b200_measure_fp32_peak(int32_t device, double *tflops);
 
 /* ---- structure read-back (parity tests) --------------------------------- */
 /*

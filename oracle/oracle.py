@@ -58,6 +58,8 @@ def lib():
         L.sbo_stream_to_csr.argtypes = [vp, vp, i32, vp, vp, i32, i32, i32, vp, vp, vp, vp]
         L.sbo_addmatmat_csr.restype = None
         L.sbo_addmatmat_csr.argtypes = [vp, vp, vp, vp, i32, i32, i32, vp, i32, i32, vp, i32, f32, f32]
+        L.sbo_addmatmat_csr_omp.restype = i32
+        L.sbo_addmatmat_csr_omp.argtypes = [vp, vp, vp, vp, i32, i32, vp, vp, f32, f32]
         L.sbo_addmatmat_csr_f64.restype = None
         L.sbo_addmatmat_csr_f64.argtypes = [vp, vp, vp, vp, i32, i32, i32, vp, i32, i32, vp, i32, f32, f32, vp, vp]
         L.sbo_transpose.restype = None
@@ -194,6 +196,11 @@ def stream_to_csr(s):
 def addmatmat_csr(row_ptr, col, code, table, T, n, k, a, m, lda, c, ldc, alpha, beta):
     lib().sbo_addmatmat_csr(_p(row_ptr), _p(col), _p(code), _p(table), T, n, k, _p(a), m, lda, _p(c), ldc, alpha, beta)
     return c
+
+
+def addmatmat_csr_omp(row_ptr, col, code, table, T, n, x, y, alpha, beta):
+    """m == 1 on all host cores (OpenMP over rows; same bits as addmatmat_csr).  Returns the thread count used."""
+    return int(lib().sbo_addmatmat_csr_omp(_p(row_ptr), _p(col), _p(code), _p(table), T, n, _p(x), _p(y), alpha, beta))
 
 
 def addmatmat_csr_f64(row_ptr, col, code, table, T, n, k, a, m, lda, c, ldc, alpha, beta):

@@ -23,6 +23,9 @@
  *   column panels of 256, per stored entry one byte of position delta and one
  *   byte of codebook index; see SURVEY.md appendix A.
  */
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
@@ -299,6 +302,30 @@ SBO_API void sbo_addmatmat_csr(const int32_t *row_ptr, const int32_t *col, const
             const int32_t r = col[e];
             for (int32_t i = 0; i < m; ++i) c[(int64_t)i * ldc + j] += a[(int64_t)i * lda + r] * w;
         }
+}
+
+/* The m == 1 case with the rows spread over all host cores (OpenMP).  NOT the reference -- the reference is
+ * single-threaded -- but the fairest CPU number for the 2^23-row power-law case, which the reference's own
+ * format cannot hold.  Every row is summed exactly as above, so the bits are the same. */
+SBO_API int32_t sbo_addmatmat_csr_omp(const int32_t *row_ptr, const int32_t *col, const uint8_t *csr_code,
+                                      const float *table, int32_t T, int32_t n, const float *x, float *y,
+                                      float alpha, float beta)
+{
+    float w_alpha[256];
+    for (int t = 0; t < 256; ++t) w_alpha[t] = (t < T) ? table[t] * alpha : 0.0f;
+    int32_t threads = 1;
+#ifdef _OPENMP
+    threads = omp_get_max_threads();
+#pragma omp parallel for schedule(dynamic, 4096)
+#endif
+    for (int32_t j = 0; j < n; ++j) {
+        float acc = y[j];
+        if (beta != 1.0) acc *= beta;
+        if (alpha != 0.0)
+            for (int32_t e = row_ptr[j]; e < row_ptr[j + 1]; ++e) acc += x[col[e]] * w_alpha[csr_code[e]];
+        y[j] = acc;
+    }
+    return threads;
 }
 
 SBO_API void sbo_addmatmat_csr_f64(const int32_t *row_ptr, const int32_t *col, const uint8_t *csr_code,

@@ -28,6 +28,11 @@ class Info(C.Structure):
     ]
 
 
+class ProductInfo(C.Structure):
+    _fields_ = [("kernel", C.c_char * 64), ("m", C.c_int32), ("reserved", C.c_int32), ("algorithmic_bytes", C.c_int64),
+                ("algorithmic_flops", C.c_int64), ("format_bytes_per_nnz", C.c_double)]
+
+
 # name -> (restype, argtypes); every symbol the two headers declare
 _vp, _i32, _i64, _f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_float
 SYMBOLS = {
@@ -40,6 +45,9 @@ SYMBOLS = {
     "sblas_b200_upload_slab": (C.c_int, [_vp, _vp, _i64, _vp, _i32, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
     "sblas_b200_upload_csr": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
     "sblas_b200_partition": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp]),
+    "sblas_b200_partition_csr": (C.c_int, [_vp, _i32, _i32, _i32, _vp]),
+    "sblas_b200_last_product": (C.c_int, [_vp, _vp]),
+    "sblas_b200_measure_fp32_peak": (C.c_int, [_i32, _vp]),
     "sblas_b200_free": (C.c_int, [_vp]),
     "sblas_b200_get_info": (C.c_int, [_vp, _vp]),
     "sblas_b200_addmatmat_host": (C.c_int, [_vp, _vp, _i32, _i32, _vp, _i32, _f32, _f32]),

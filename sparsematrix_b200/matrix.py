@@ -176,6 +176,13 @@ class DeviceMatrix:
         _capi.check(_capi.lib().sblas_b200_profile_end(self._h, C.byref(ms), C.byref(cnt)))
         return ms.value, cnt.value
 
+    def last_product(self):
+        """sblas_b200_last_product: dominant kernel and algorithmic bytes / flops of the most recent product."""
+        pi = _capi.ProductInfo()
+        _capi.check(_capi.lib().sblas_b200_last_product(self._h, C.byref(pi)))
+        return {"kernel": pi.kernel.decode(), "m": pi.m, "algorithmic_bytes": pi.algorithmic_bytes,
+                "algorithmic_flops": pi.algorithmic_flops, "format_bytes_per_nnz": pi.format_bytes_per_nnz}
+
     # ---- structure read-back ----------------------------------------------------------------
     def decode_dense(self, stride, trans=False):
         inf = self.info()
@@ -218,6 +225,21 @@ def partition(block_bounds, block_index_bounds, cols, parts):
     out = np.zeros(parts + 1, np.int32)
     _capi.check(_capi.lib().sblas_b200_partition(_ptr(bb), _ptr(bib), bb.shape[0], cols, parts, _ptr(out)))
     return out
+
+
+def partition_csr(row_ptr, parts, align=256):
+    """sblas_b200_partition_csr: nnz-balanced row splits of a CSR matrix, interior values multiples of `align`."""
+    row_ptr = np.ascontiguousarray(row_ptr, np.int32)
+    out = np.zeros(parts + 1, np.int32)
+    _capi.check(_capi.lib().sblas_b200_partition_csr(_ptr(row_ptr), row_ptr.shape[0] - 1, parts, align, _ptr(out)))
+    return out
+
+
+def measure_fp32_peak(device=0):
+    """sblas_b200_measure_fp32_peak: TFLOP/s of register-resident fp32 FMA chains on `device`."""
+    t = C.c_double(0.0)
+    _capi.check(_capi.lib().sblas_b200_measure_fp32_peak(device, C.byref(t)))
+    return t.value
 
 
 class SparseMatrix:

@@ -13,6 +13,7 @@
 // and then multiplies even for beta == 0; alpha == 0 means "scale only" (:152).
 #include <stdio.h>
 #include <stdlib.h>
+#include <string.h>
 
 #include <algorithm>
 
@@ -336,6 +337,9 @@ static int x_load_mode(const sblas_b200_matrix *mat) {
 template <int LPR, bool RED>
 static void launch_spmv_rows(const sblas_b200_matrix *mat, const float *x, float *y, float alpha, float beta, int xcg,
                              cudaStream_t stream) {
+    char name[64];
+    snprintf(name, sizeof(name), "%s<%d>%s", mat->d_row_order ? "spmv_sorted" : "spmv_rows", LPR, RED ? " red" : "");
+    note_product(const_cast<sblas_b200_matrix *>(mat), name, 1, 5.0, mat->d_row_order ? (int64_t)12 * mat->n : (int64_t)4 * (mat->n + 1));
     if (mat->d_row_order) {                                 // skewed row lengths: the sorted copy
         const size_t threads = (size_t)mat->n_ordered * LPR;
         SB_LAUNCH((spmv_sorted_kernel<LPR, RED>), (unsigned)((threads + 255) / 256), 256, 0, stream, mat->d_sblk_ptr, mat->d_slen,
@@ -363,7 +367,14 @@ static int run_spmv(sblas_b200_matrix *mat, const float *x, float *y, float alph
     if (!staged && mat->d_row_order && is_peer_pointer(y)) return run_spmv_sorted_to_peer(mat, x, y, alpha, beta, stream);
     const int xcg = x_load_mode(mat);
     const bool red = beta == 1.0f && is_peer_pointer(y);    // y across NVLink: add at the owner, do not read it
-    {
+    // huge x, scattered columns: the column-blocked copy in two streaming passes (spmv_blocked.cu); it applies beta to
+    // every row, so the long rows below only add their sums
+    const bool blocked = !staged && mat->blocked.state == 1;
+    if (blocked) {
+        const int brc = run_spmv_blocked(mat, x, y, alpha, beta, red, stream);
+        if (brc != SBLAS_B200_OK) return brc;
+        beta = 1.0f;
+    } else {
     KernelTimer timer(mat, stream);
 #define SB_SPMV_CASE(L) \
     case L: red ? launch_spmv_rows<L, true>(mat, x, y, alpha, beta, xcg, stream) \
@@ -397,6 +408,9 @@ template <int LPN>
 static void launch_spmm_gather(const sblas_b200_matrix *mat, const float *xt, int mp, float *c, int ldc, int m,
                                float alpha, float beta, cudaStream_t stream) {
     const dim3 grid((mat->n + 31) / 32, (m + 4 * LPN - 1) / (4 * LPN));
+    char name[64];
+    snprintf(name, sizeof(name), "spmm_gather<%d>", LPN);
+    note_product(const_cast<sblas_b200_matrix *>(mat), name, m, 5.0, (int64_t)4 * (mat->n + 1));
     SB_LAUNCH(spmm_gather_kernel<LPN>, grid, 256, 0, stream, mat->d_row_ptr, mat->d_col, mat->d_code, mat->d_table,
               mat->T, xt, mp, c, ldc, mat->n, m, alpha, beta);
 }
@@ -763,6 +777,17 @@ int sblas_b200_addmatmat_dev(sblas_b200_matrix *mat, const float *d_a, int32_t m
     if (!scope.ok()) return SBLAS_B200_ECUDA;
     std::lock_guard<std::mutex> guard(mat->lock);
     return product_on_stream(mat, d_a, m, lda, d_c, ldc, alpha, beta, static_cast<cudaStream_t>(stream));
+}
+
+int sblas_b200_last_product(const sblas_b200_matrix *mat, sblas_b200_product_info *out) {
+    if (!mat || !out) return fail(SBLAS_B200_EINVAL, "null argument");
+    memset(out, 0, sizeof(*out));
+    memcpy(out->kernel, mat->last_kernel, sizeof(out->kernel));
+    out->m = mat->last_m;
+    out->algorithmic_bytes = mat->last_bytes;
+    out->algorithmic_flops = (int64_t)2 * mat->nnz * mat->last_m;
+    out->format_bytes_per_nnz = mat->last_bytes_per_nnz;
+    return SBLAS_B200_OK;
 }
 
 int sblas_b200_profile_begin(sblas_b200_matrix *mat) {

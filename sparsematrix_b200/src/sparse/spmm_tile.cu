@@ -433,6 +433,11 @@ static int launch_tile(const sblas_b200_matrix *mat, const TileFormat &tf, const
         configured = true;
     }
     const dim3 grid(((tf.ngroups + nwarps - 1) / nwarps) * ((m + MT - 1) / MT));
+    {
+        char name[64];
+        snprintf(name, sizeof(name), "spmm_tile<%d,%d,%d,%d>x%d%s", RS, NF4, STAGES, SPLIT, nwarps, (epi & kEpiRedAdd) ? " red" : "");
+        note_product(const_cast<sblas_b200_matrix *>(mat), name, m, 5.0, (int64_t)4 * (mat->n + 1) + (int64_t)8 * tf.ngroups * tf.nchunks);
+    }
 #ifdef EXP_TIMELINE
     { static bool reg = false; if (!reg) { atexit(dump_timeline); reg = true; } g_tl_ctas = grid.x; }
 #endif

@@ -241,6 +241,7 @@ int run_spmv_dense(sblas_b200_matrix *mat, const float *x, float *y, float alpha
         }
         ~Timer() { if (a) { cudaEventRecord(b, st); mat->prof_events.push_back(std::make_pair(a, b)); } }
     } timer(mat, stream);
+    note_product(mat, "spmv_dense", 1, (double)mat->n * (double)mat->dense_kpad / (double)mat->nnz, (int64_t)4 * (mat->n + 1));
     SB_LAUNCH(spmv_dense_kernel, grid, colwarps * rowsplit * 32, smem, stream, mat->d_dense_code, mat->dense_kpad, mat->d_row_ptr,
               mat->d_table, mat->T, x, y, mat->n, mat->k, alpha, beta, rows_per_cta, colwarps, pf_groups, is_peer_pointer(y) ? 1 : 0);
     SB_CHECK_LAUNCH();

@@ -64,6 +64,13 @@ DeviceScope::~DeviceScope() {
     if (prev_ >= 0) cudaSetDevice(prev_);
 }
 
+void note_product(sblas_b200_matrix *mat, const char *kernel, int m, double bytes_per_nnz, int64_t index_bytes) {
+    snprintf(mat->last_kernel, sizeof(mat->last_kernel), "%s", kernel);
+    mat->last_m = m;
+    mat->last_bytes_per_nnz = bytes_per_nnz;
+    mat->last_bytes = (int64_t)(bytes_per_nnz * (double)mat->nnz + 0.5) + index_bytes + (int64_t)4 * mat->k * m + (int64_t)8 * mat->n * m;
+}
+
 int ensure_buffer(float **buf, size_t *have, size_t need) {
     if (need <= *have) return SBLAS_B200_OK;
     if (*buf) { cudaFree(*buf); *buf = nullptr; *have = 0; }
@@ -352,6 +359,12 @@ int plan_spmv(sblas_b200_matrix *mat, const int32_t *h_row_ptr) {
     // decreasing length (counting sort) and a warp's rows are about equally long.
     bool sort_rows = n >= 65536 && (double)max_len >= 4.0 * std::max(1.0, mean);
     if (const char *env = getenv("SBLAS_B200_SORT_ROWS")) sort_rows = env[0] == '1';
+    // x of many megabytes and scattered columns: the column-blocked copy replaces the sorted one (blocked_format.cu)
+    {
+        const int brc = build_blocked_format(mat);
+        if (brc != SBLAS_B200_OK) return brc;
+        if (mat->blocked.state == 1) sort_rows = false;
+    }
     if (sort_rows) {
         const int32_t cap = mat->long_threshold;
         std::vector<int32_t> count((size_t)cap + 2, 0), order;
@@ -430,6 +443,8 @@ static void release(sblas_b200_matrix *mat) {
     for (TileFormat &tf : mat->tile) { cudaFree(tf.d_blocks); cudaFree(tf.d_grp_ptr); cudaFree(tf.d_grp_nq); }
     cudaFree(mat->d_ws); cudaFree(mat->d_partial); cudaFree(mat->d_host_a); cudaFree(mat->d_host_c);
     cudaFree(mat->d_host_p); cudaFree(mat->d_dense_code); cudaFree(mat->d_peer_y);
+    cudaFree(mat->blocked.d_lcol); cudaFree(mat->blocked.d_lrow); cudaFree(mat->blocked.d_code);
+    cudaFree(mat->blocked.d_seg_ptr); cudaFree(mat->blocked.d_cb_start); cudaFree(mat->blocked.d_prod);
     if (mat->stream) cudaStreamDestroy(mat->stream);
     if (mat->ws_event) cudaEventDestroy(mat->ws_event);
     if (mat->stream2) cudaStreamDestroy(mat->stream2);
@@ -690,6 +705,27 @@ int sblas_b200_partition(const int32_t *block_bounds, const int32_t *block_index
         col_splits[g] = std::min(cols, b * kPanelWidth);
     }
     col_splits[parts] = cols;
+    return SBLAS_B200_OK;
+}
+
+int sblas_b200_partition_csr(const int32_t *row_ptr, int32_t n, int32_t parts, int32_t align, int32_t *row_splits) {
+    if (!row_ptr || n < 0 || parts < 1 || align < 1 || (align & (align - 1)) || !row_splits)
+        return fail(SBLAS_B200_EINVAL, "bad partition arguments");
+    const int64_t total = row_ptr[n];
+    row_splits[0] = 0;
+    int prev = 0;
+    for (int g = 1; g < parts; ++g) {
+        // aligned row whose prefix is closest to the ideal share, never moving backwards
+        const int64_t target = (int64_t)((double)total * g / parts + 0.5);
+        int r = (int)(std::lower_bound(row_ptr, row_ptr + n + 1, (int32_t)std::min<int64_t>(target, total)) - row_ptr);
+        int lo = r / align * align, hi = std::min<int64_t>(n, (int64_t)lo + align);
+        if (hi == n && (n % align)) hi = lo;                  // interior splits stay aligned
+        r = (target - row_ptr[lo] <= (int64_t)row_ptr[hi] - target) ? lo : hi;
+        if (r < prev) r = prev;
+        prev = r;
+        row_splits[g] = r;
+    }
+    row_splits[parts] = n;
     return SBLAS_B200_OK;
 }
 

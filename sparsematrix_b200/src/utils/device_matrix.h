@@ -72,6 +72,26 @@ struct TileFormat {
     int64_t nblocks = 0;
 };
 
+// Column-blocked SpMV layout for matrices whose x gathers would each cost an L2 sector (k beyond any L1, columns
+// spread over all of it): the entries of the rows up to long_threshold, sorted by (column block, row, column).
+// Pass 1 streams them with the block's x tile in shared memory and writes one product per entry, pass 2 adds
+// the products of a row sub-block (one warp) in stream order (src/utils/blocked_format.cu, src/sparse/spmv_blocked.cu).
+struct BlockedFormat {
+    int state = 0;                      // 0 = not built, 1 = built, -1 = not applicable to this matrix
+    int cbw = 0;                        // columns per block = floats of x held in shared memory by pass 1
+    int ncb = 0;                        // column blocks
+    int rs = 0, nsub = 0;               // rows per sub-block (one warp of pass 2), number of sub-blocks
+    int64_t total = 0;                  // stream slots: a column block starts on a multiple of 32, a sub-segment on one of 4
+    int64_t entries = 0;                // real entries among them
+    int64_t runs = 0;                   // maximal groups of stream neighbours that share a row
+    uint16_t *d_lcol = nullptr;         // [total] column inside the block
+    uint16_t *d_lrow = nullptr;         // [total] row inside the sub-block (0xffff in padding slots)
+    uint8_t *d_code = nullptr;          // [total] codebook index (255 in padding slots)
+    int32_t *d_seg_ptr = nullptr;       // [ncb][nsub + 1] first slot of (block, sub-block); [.][nsub] = end of the block's entries
+    int32_t *d_cb_start = nullptr;      // [ncb + 1] first slot of a block
+    float *d_prod = nullptr;            // [total] products, written by pass 1 and read by pass 2 of the same call
+};
+
 struct sblas_b200_matrix {
     int device = 0;
     int32_t k = 0;           // rows of S  = length of an X row index space
@@ -140,6 +160,14 @@ struct sblas_b200_matrix {
     int64_t dense_kpad = 0;
     int dense_state = 0;                // 0 = not built yet, 1 = built, -1 = not possible (memory)
 
+    BlockedFormat blocked;
+
+    // sblas_b200_last_product: what the most recent product launched as its dominant kernel
+    char last_kernel[64] = "";
+    int32_t last_m = 0;
+    int64_t last_bytes = 0;
+    double last_bytes_per_nnz = 0.0;
+
     // sblas_b200_profile_begin/_end: event pairs around the dominant kernel
     bool profiling = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t> > prof_events;
@@ -162,6 +190,14 @@ int run_spmm_tile(sblas_b200_matrix *mat, const float *d_a, int m, int lda, floa
                   float beta, cudaStream_t stream);
 // src/sparse/spmv_dense.cu: 0 = done, 1 = not applicable (use the row kernels), < 0 = error
 int run_spmv_dense(sblas_b200_matrix *mat, const float *x, float *y, float alpha, float beta, cudaStream_t stream);
+constexpr int kBlockedMaxRows = 1792;   // rows per sub-block at most: 16 warps x 1792 floats = 112 KB, two CTAs per SM
+// src/utils/blocked_format.cu: 0 = built or not applicable (see blocked.state), < 0 = error
+int build_blocked_format(sblas_b200_matrix *mat);
+// src/sparse/spmv_blocked.cu: the rows up to long_threshold; the caller adds the long rows afterwards (beta already applied)
+int run_spmv_blocked(sblas_b200_matrix *mat, const float *x, float *y, float alpha, float beta, bool red, cudaStream_t stream);
+// records the dominant kernel of the running product: name, bytes of the device format per non-zero, and the bytes per
+// launch that do not scale with nnz besides X and C (row pointers, segment pointers, ...)
+void note_product(sblas_b200_matrix *mat, const char *kernel, int m, double bytes_per_nnz, int64_t index_bytes);
 // src/sparse/product.cu
 int product_on_stream(sblas_b200_matrix *mat, const float *d_a, int32_t m, int32_t lda, float *d_c, int32_t ldc,
                       float alpha, float beta, cudaStream_t stream);

@@ -889,3 +889,89 @@ def test_products_can_be_captured_into_a_cuda_graph_and_replayed():
     dev.addmatmat_dev(a[8], 8, k, c1, n, 1.0, 1.0)
     torch.cuda.synchronize()
     assert_bits_equal(c1.cpu().numpy(), want[8], "eager after capture")
+
+
+# ------------------------------------------------------------------ column-blocked two-pass SpMV (spmv_blocked.cu)
+def _blocked_upload(row_ptr, col, code, tab, n, k, cbw, rs, long_threshold=None):
+    def up():
+        return sb.DeviceMatrix.upload_csr(row_ptr, col, code, tab, 255, n, k)
+    fn = lambda: _with_env("SBLAS_B200_BLOCKED_CBW", str(cbw), lambda: _with_env("SBLAS_B200_BLOCKED_RS", str(rs), up))
+    if long_threshold is not None:
+        inner = fn
+        fn = lambda: _with_env("SBLAS_B200_LONG_THRESHOLD", str(long_threshold), inner)
+    return _with_env("SBLAS_B200_SPMV_BLOCKED", "1", fn)
+
+
+@pytest.mark.parametrize("n,k,cbw,rs,x_min,cap,long_threshold", [
+    (5000, 3001, 256, 37, 4, 900, None),        # tail column block, runs of equal rows across lanes, n not a multiple of rs
+    (70001, 40000, 4096, 100, 8, 30000, 500),   # long rows (split-row path) beside the blocked ones
+    (300, 100000, 32768, 1, 2, 64, None),       # one row per sub-block, default tile width
+    (4097, 513, 64, 1792, 16, 513, None),       # widest sub-block, rows as long as k
+])
+def test_blocked_spmv_against_the_oracle_and_the_row_kernels(n, k, cbw, rs, x_min, cap, long_threshold):
+    import torch
+    row_ptr, col, code = gen.powerlaw_csr(n, k, seed=77, x_min=x_min, cap=cap)
+    lens = np.diff(row_ptr).astype(np.int64)                   # a few rows lose their entries, incl. the last one
+    keep = np.ones(col.shape[0], bool)
+    for j in (0, 5, 6, n - 1):
+        keep[row_ptr[j]:row_ptr[j + 1]] = False; lens[j] = 0
+    col, code = col[keep], code[keep]
+    row_ptr = np.concatenate(([0], np.cumsum(lens))).astype(np.int32)
+    tab = gen.codebook()
+    dev = _blocked_upload(row_ptr, col, code, tab, n, k, cbw, rs, long_threshold=long_threshold)
+    plain = _with_env("SBLAS_B200_SPMV_BLOCKED", "0", lambda: sb.DeviceMatrix.upload_csr(row_ptr, col, code, tab, 255, n, k))
+    if long_threshold:
+        assert dev.info().long_rows > 0
+    a = gen.dense_uniform((1, k), 1); c0 = gen.dense_uniform((1, n), 2); c0[0, 5] = -0.0
+    for alpha, beta in ((1.0, 1.0), (1.3, 2.0), (0.7, 0.0)):
+        got = dev.addmatmat_host(a, 1, k, c0.copy(), n, alpha, beta)
+        lp = dev.last_product()
+        assert lp["kernel"].startswith("spmv_blocked") and lp["m"] == 1 and lp["algorithmic_flops"] == 2 * int(row_ptr[-1]), lp
+        y64, bound = O.addmatmat_csr_f64(row_ptr, col, code, tab, 255, n, k, a, 1, k, c0, n, alpha, beta)
+        back = O.error_measures(got, 1, n, n, y64, bound)[0]
+        want = O.addmatmat_csr(row_ptr, col, code, tab, 255, n, k, a, 1, k, c0.copy(), n, alpha, beta)
+        rback = O.error_measures(want, 1, n, n, y64, bound)[0]
+        assert back <= TOL, (alpha, beta, back, rback)
+        # rows without entries: exactly the scaled value, sign of zero kept (the reference's own bits)
+        for j in (0, 5, 6, n - 1):
+            assert got.reshape(-1)[j].tobytes() == want.reshape(-1)[j].tobytes(), (j, alpha, beta)
+        other = plain.addmatmat_host(a, 1, k, c0.copy(), n, alpha, beta)
+        assert O.error_measures(other, 1, n, n, y64, bound)[0] <= TOL
+        assert not plain.last_product()["kernel"].startswith("spmv_blocked")
+        assert_bits_equal(dev.addmatmat_host(a, 1, k, c0.copy(), n, alpha, beta), got, "run-to-run determinism")
+    # x off the 16-byte grid (scalar tile loads) and y declared peer memory (sums added by reductions, y never read)
+    L = sb.lib()
+    xbuf = torch.zeros(k + 1, device="cuda"); xbuf[1:] = torch.from_numpy(a.reshape(-1)).cuda()
+    for alpha, beta in ((1.0, 1.0), (1.3, 2.0)):
+        want = torch.from_numpy(c0.copy()).cuda()
+        dev.addmatmat_dev(torch.from_numpy(a).cuda(), 1, k, want, n, alpha, beta)
+        got = torch.from_numpy(c0.copy()).cuda()
+        dev.addmatmat_dev(xbuf[1:], 1, k, got, n, alpha, beta)
+        torch.cuda.synchronize()
+        assert_bits_equal(got.cpu().numpy(), want.cpu().numpy(), "misaligned x")
+        buf = torch.from_numpy(c0.copy()).cuda()
+        assert L.sblas_b200_peer_register(C.c_void_p(buf.data_ptr()), buf.numel() * 4) == _capi.OK
+        try:
+            dev.addmatmat_dev(torch.from_numpy(a).cuda(), 1, k, buf, n, alpha, beta)
+            torch.cuda.synchronize()
+        finally:
+            assert L.sblas_b200_peer_unregister(C.c_void_p(buf.data_ptr())) == _capi.OK
+        assert_bits_equal(buf.cpu().numpy(), want.cpu().numpy(), f"peer range alpha={alpha} beta={beta}")
+
+
+def test_blocked_spmv_is_built_only_on_request_for_small_matrices():
+    # a band: every row's entries share one column block -> the row kernels' gathers hit L1, the second copy would lose
+    n = k = 1 << 16
+    lens = np.full(n, 8, np.int64)
+    row_ptr = np.concatenate(([0], np.cumsum(lens))).astype(np.int32)
+    col = (np.repeat(np.arange(n, dtype=np.int64), 8) + np.tile(np.arange(8, dtype=np.int64), n)) % k
+    col = np.sort(col.reshape(n, 8), axis=1).reshape(-1).astype(np.int32)
+    code = (np.arange(col.shape[0]) % 255).astype(np.uint8)
+    tab = gen.codebook()
+    dev = _with_env("SBLAS_B200_SPMV_BLOCKED", "1", lambda: sb.DeviceMatrix.upload_csr(row_ptr, col, code, tab, 255, n, k))
+    a = gen.dense_uniform((1, k), 1)
+    dev.addmatmat_host(a, 1, k, np.zeros((1, n), np.float32), n, 1.0, 1.0)
+    assert dev.last_product()["kernel"].startswith("spmv_blocked")          # forced: built whatever the shape
+    dev = sb.DeviceMatrix.upload_csr(row_ptr, col, code, tab, 255, n, k)
+    dev.addmatmat_host(a, 1, k, np.zeros((1, n), np.float32), n, 1.0, 1.0)
+    assert dev.last_product()["kernel"].startswith("spmv_rows")              # small: the row kernels stay

@@ -196,3 +196,23 @@ def test_save_and_load_round_trip_and_reject_corruption(tmp_path):
     F = sb.SparseMatrix(codes, n, k, k, tab, 255, 0)
     F.Load(str(tmp_path / "empty.sblas"))
     assert F == E and F.NumRows() == 0 and F.NumCols() == 0
+
+
+def test_partition_csr_balances_nnz_on_aligned_rows():
+    # the CSR analogue of sblas_b200_partition (config 4 cannot go through the panel format): nnz-balanced, aligned splits
+    n = 100000
+    lens = gen.powerlaw_row_lengths(n, seed=5, x_min=8, cap=1 << 14)
+    row_ptr = np.concatenate(([0], np.cumsum(lens))).astype(np.int32)
+    for parts in (1, 2, 3, 8):
+        sp = sb.partition_csr(row_ptr, parts, 256)
+        assert sp[0] == 0 and sp[-1] == n and np.all(np.diff(sp) >= 0)
+        assert np.all(sp[1:-1] % 256 == 0)
+        share = np.diff(row_ptr[sp].astype(np.int64))
+        assert share.sum() == row_ptr[-1]
+        assert share.max() <= row_ptr[-1] / parts + 256 * lens.max()          # within one aligned step of the ideal share
+    # everything in one row: the other slabs are empty, never negative
+    rp = np.zeros(1001, np.int32); rp[501:] = 7777
+    sp = sb.partition_csr(rp, 4, 256)
+    assert sp[0] == 0 and sp[-1] == 1000 and np.all(np.diff(sp) >= 0)
+    with pytest.raises(sb.SblasError):
+        sb.partition_csr(row_ptr, 2, 100)                                     # alignment must be a power of two

@@ -156,3 +156,76 @@ def model_scaling_ceiling(nnz, n, k, m, world_size, bytes_per_nnz=5):
     one = bytes_per_nnz * nnz + 4 * (n + 1) + 4 * k * m + 8 * n * m
     per = bytes_per_nnz * nnz / world_size + 4 * (n / world_size + 1) + 4 * k * m + 8 * n * m / world_size
     return one / per
+
+
+def csr_slab(row_ptr, col, code, lo, hi):
+    """Rows [lo, hi) of a CSR matrix as their own CSR (row_ptr rebased to 0): what ``sblas_b200_upload_csr`` takes for one slab."""
+    row_ptr = np.asarray(row_ptr)
+    e0, e1 = int(row_ptr[lo]), int(row_ptr[hi])
+    rp = (row_ptr[lo:hi + 1].astype(np.int64) - e0).astype(np.int32)
+    return np.ascontiguousarray(rp), np.ascontiguousarray(col[e0:e1]), np.ascontiguousarray(code[e0:e1])
+
+
+class ShardedMatrix:
+    """One matrix cut into nnz-balanced row slabs of W, slab r resident on rank r's GPU, X replicated.
+
+    Built on every rank from the same host data -- a ``SparseMatrix`` (panel streams: ``sblas_b200_partition`` +
+    ``sblas_b200_upload_slab``) or a CSR triple (``sblas_b200_partition_csr`` + ``sblas_b200_upload_csr``).
+    ``product_into(out, d_a, ...)`` is the strong-scaled step: this rank's product stored straight into the
+    ``PeerOutput`` on the root GPU.  ``addmatmat_host`` is the host-buffer entry point of a rank: every rank owns a
+    full copy of A in host memory, uploads only its 1/world share over its own PCIe link and receives the rest over
+    NVLink (all-gather), multiplies its slab and copies its C slab back."""
+
+    def __init__(self, source, rank, world, device, table=None, T=255, k=None, align=256):
+        self.rank, self.world, self.device = rank, world, device
+        if isinstance(source, SparseMatrix):
+            self.n, self.k = source.NumCols(), source.NumRows()
+            self.splits = slab_bounds(source, world)
+            self.lo, self.hi = int(self.splits[rank]), int(self.splits[rank + 1])
+            self.mat = source.upload_slab(self.lo, self.hi, device) if self.hi > self.lo else None
+        else:
+            from .matrix import partition_csr
+            row_ptr, col, code = source
+            self.n, self.k = int(len(row_ptr) - 1), int(k)
+            self.splits = partition_csr(row_ptr, world, align)
+            self.lo, self.hi = int(self.splits[rank]), int(self.splits[rank + 1])
+            self.mat = None
+            if self.hi > self.lo:
+                rp, c, cd = csr_slab(row_ptr, col, code, self.lo, self.hi)
+                self.mat = DeviceMatrix.upload_csr(rp, c, cd, table, T, self.hi - self.lo, self.k, device)
+        self.nnz_local = int(self.mat.nnz) if self.mat is not None else 0
+        self._stage = {}
+
+    def product_into(self, out, d_a, m, alpha, beta, stream=0):
+        if self.mat is not None:
+            out.write_slab(self.mat, d_a, self.k, self.lo, alpha, beta, stream=stream)
+
+    def product_local(self, d_a, m, d_c_slab, alpha, beta, stream=0):
+        if self.mat is not None:
+            self.mat.addmatmat_dev(d_a, m, self.k, d_c_slab, self.hi - self.lo, alpha, beta, stream=stream)
+
+    def addmatmat_host(self, h_a, m, h_c_slab, alpha, beta):
+        """h_a: pinned torch tensor m x k (the same on every rank); h_c_slab: pinned m x (hi - lo), updated in place."""
+        import torch
+        import torch.distributed as dist
+        dev = torch.device("cuda", self.device)
+        total = m * self.k
+        share = (total + self.world - 1) // self.world
+        if m not in self._stage:
+            self._stage[m] = (torch.empty(share * self.world, dtype=torch.float32, device=dev),
+                              torch.empty(share, dtype=torch.float32, device=dev),
+                              torch.empty((m, max(1, self.hi - self.lo)), dtype=torch.float32, device=dev))
+        d_full, d_part, d_c = self._stage[m]
+        flat = h_a.view(-1)
+        b, e = min(total, self.rank * share), min(total, (self.rank + 1) * share)
+        if e > b:
+            d_part[: e - b].copy_(flat[b:e], non_blocking=True)          # this rank's share of A over its own PCIe link
+        if self.hi > self.lo:
+            d_c.copy_(h_c_slab, non_blocking=True)
+        dist.all_gather_into_tensor(d_full, d_part)                      # the rest of A over NVLink
+        if self.mat is not None:
+            self.mat.addmatmat_dev(d_full, m, self.k, d_c, self.hi - self.lo, alpha, beta,
+                                   stream=torch.cuda.current_stream().cuda_stream)
+            h_c_slab.copy_(d_c, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return h_c_slab

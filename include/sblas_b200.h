@@ -190,6 +190,29 @@ SBLAS_B200_API int sblas_b200_addmatmat_host(sblas_b200_matrix *mat, const float
 SBLAS_B200_API int sblas_b200_addmatmat_dev(sblas_b200_matrix *mat, const float *d_a, int32_t m, int32_t lda,
                                             float *d_c, int32_t ldc, float alpha, float beta, void *stream);
 
+/*
+ * The same product for callers that cannot allocate (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  This entry
+ * point has NO counterpart in the reference.
+ * It calls no cudaMalloc / cudaFree / allocating routine, ever:
+ * the product runs as transpose (X = A^T) + the gather-form kernel on the CSR the
+ * upload left on the device, with X staged in ONE fixed device array of
+ * SBLAS_B200_NOALLOC_MAX_FLOATS floats (4 MiB) that every GPU which loads the
+ * library holds until exit.  Limit: k * round_up(m, 4) <= SBLAS_B200_NOALLOC_MAX_FLOATS
+ * (e.g. k = 4096 with m <= 256, k = 16384 with m <= 64); beyond it the call fails
+ * with SBLAS_B200_EINVAL and a message naming the limit, and nothing is enqueued.
+ * All calls on one device share the array: calls that overlap on the GPU
+ * (different streams, or different handles, without ordering between them) RACE on it
+ * -- keep them on one stream or order them yourself.  The array keeps the previous
+ * call's contents; nothing in it needs to start at zero, each call rewrites every
+ * float it later reads (padding columns included) before reading it.  Arguments,
+ * semantics and results are those of sblas_b200_addmatmat_dev() (results may differ
+ * from it in rounding where that picks another kernel: same 1e-5 backward bound).
+ */
+#define SBLAS_B200_NOALLOC_MAX_FLOATS (1 << 20)
+SBLAS_B200_API int sblas_b200_addmatmat_dev_noalloc(sblas_b200_matrix *mat, const float *d_a, int32_t m, int32_t lda,
+                                                    float *d_c, int32_t ldc, float alpha, float beta, void *stream);
+
 /* ---- the reference's free kernel functions (src/sparse/kernel.h:42-62) ------ */
 /*
  * For callers that use the reference's free functions directly.  Host pointers,

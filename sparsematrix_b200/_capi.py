@@ -51,6 +51,7 @@ SYMBOLS = {
     "sblas_b200_free": (C.c_int, [_vp]),
     "sblas_b200_get_info": (C.c_int, [_vp, _vp]),
     "sblas_b200_addmatmat_host": (C.c_int, [_vp, _vp, _i32, _i32, _vp, _i32, _f32, _f32]),
+    "sblas_b200_addmatmat_dev_noalloc": (C.c_int, [_vp, _vp, _i32, _i32, _vp, _i32, _f32, _f32, _vp]),
     "sblas_b200_addmatmat_dev": (C.c_int, [_vp, _vp, _i32, _i32, _vp, _i32, _f32, _f32, _vp]),
     "sblas_b200_profile_begin": (C.c_int, [_vp]),
     "sblas_b200_profile_end": (C.c_int, [_vp, _vp, _vp]),

@@ -167,6 +167,15 @@ class DeviceMatrix:
         _capi.check(_capi.lib().sblas_b200_addmatmat_dev(self._h, _ptr(d_a), m, lda, _ptr(d_c), ldc, alpha, beta,
                                                          C.c_void_p(stream) if stream else None))
 
+    def addmatmat_dev_noalloc(self, d_a, m, lda, d_c, ldc, alpha, beta, stream=0):
+        """sblas_b200_addmatmat_dev_noalloc: the same product without any allocation (fixed 4 MiB staging array,
+        k * round_up(m, 4) <= 2^20); calls that overlap on one GPU race on that array."""
+        if m > 0:
+            n, k = self._shape()
+            _need(d_a, (m - 1) * lda + k, "d_a"); _need(d_c, (m - 1) * ldc + n, "d_c")
+        _capi.check(_capi.lib().sblas_b200_addmatmat_dev_noalloc(self._h, _ptr(d_a), m, lda, _ptr(d_c), ldc, alpha, beta,
+                                                                 C.c_void_p(stream) if stream else None))
+
     def profile_begin(self):
         _capi.check(_capi.lib().sblas_b200_profile_begin(self._h))
 

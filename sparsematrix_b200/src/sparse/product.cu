@@ -763,6 +763,65 @@ static int host_product_direct(sblas_b200_matrix *mat, const float *a_mapped, fl
     return SBLAS_B200_OK;
 }
 
+// ---- product without any allocation (sblas_b200_addmatmat_dev_noalloc) ------------------------
+// For callers that cannot allocate (stream capture, tight serving loops): the gather-form product above with its
+// X = A^T staging in a fixed device array instead of the handle's workspace.  The array's name is a host-side
+// stand-in in host code, not a device address: its address is fetched once per device with
+// cudaGetSymbolAddress (that device current) and handed to the kernels.  Every call on a device shares the
+// array; it keeps the previous call's contents, which is harmless: transpose_in_kernel rewrites all k x mp
+// floats the gather kernel reads (padding columns as zeros) before that kernel starts, on the same stream.
+static __device__ __align__(256) float g_noalloc_scratch[SBLAS_B200_NOALLOC_MAX_FLOATS];
+
+static int noalloc_scratch(int device, float **out) {
+    static std::mutex lock;
+    static float *ptr_on[64] = {nullptr};
+    if (device < 0 || device >= 64) return fail(SBLAS_B200_EINVAL, "device %d outside [0, 64)", device);
+    std::lock_guard<std::mutex> guard(lock);
+    if (!ptr_on[device]) {                                  // set-up, once per device; `device` is current (DeviceScope)
+        float *p = nullptr;
+        SB_CUDA(cudaGetSymbolAddress((void **)&p, g_noalloc_scratch));
+        ptr_on[device] = p;
+    }
+    *out = ptr_on[device];
+    return SBLAS_B200_OK;
+}
+
+static int product_noalloc(sblas_b200_matrix *mat, const float *d_a, int m, int lda, float *d_c, int ldc, float alpha,
+                           float beta, cudaStream_t stream) {
+    const int n = mat->n;
+    if (m == 0 || n == 0) return SBLAS_B200_OK;
+    if (alpha == 0.0f || mat->nnz == 0) {                   // sparse-matrix.cc:149-152: only the beta scale remains
+        if (beta != 1.0f) {
+            const dim3 grid((n + 255) / 256, std::min(m, 1024));
+            SB_LAUNCH(scale_kernel, grid, 256, 0, stream, d_c, m, n, ldc, beta);
+            SB_CHECK_LAUNCH();
+        }
+        return SBLAS_B200_OK;
+    }
+    const int mp = (m + 3) & ~3;
+    if ((int64_t)mat->k * mp > (int64_t)SBLAS_B200_NOALLOC_MAX_FLOATS)
+        return fail(SBLAS_B200_EINVAL, "sblas_b200_addmatmat_dev_noalloc: k * round_up(m, 4) = %lld floats exceeds the fixed "
+                    "scratch of %lld floats (SBLAS_B200_NOALLOC_MAX_FLOATS); use sblas_b200_addmatmat_dev",
+                    (long long)mat->k * mp, (long long)SBLAS_B200_NOALLOC_MAX_FLOATS);
+    float *xt = nullptr;
+    const int rc = noalloc_scratch(mat->device, &xt);
+    if (rc != SBLAS_B200_OK) return rc;
+    const dim3 tgrid((mat->k + 31) / 32, (mp + 31) / 32);
+    SB_LAUNCH(transpose_in_kernel, tgrid, 256, 0, stream, d_a, m, mat->k, lda, xt, mp);
+#define SB_NOALLOC_GATHER(LPN)                                                                                   \
+    SB_LAUNCH(spmm_gather_kernel<LPN>, dim3((n + 31) / 32, (m + 4 * LPN - 1) / (4 * LPN)), 256, 0, stream,       \
+              mat->d_row_ptr, mat->d_col, mat->d_code, mat->d_table, mat->T, xt, mp, d_c, ldc, n, m, alpha, beta)
+    if (mp <= 4) SB_NOALLOC_GATHER(1);
+    else if (mp <= 8) SB_NOALLOC_GATHER(2);
+    else if (mp <= 16) SB_NOALLOC_GATHER(4);
+    else if (mp <= 32) SB_NOALLOC_GATHER(8);
+    else if (mp <= 64) SB_NOALLOC_GATHER(16);
+    else SB_NOALLOC_GATHER(32);
+#undef SB_NOALLOC_GATHER
+    SB_CHECK_LAUNCH();
+    return SBLAS_B200_OK;
+}
+
 }  // namespace sblas_b200
 
 using namespace sblas_b200;
@@ -777,6 +836,15 @@ int sblas_b200_addmatmat_dev(sblas_b200_matrix *mat, const float *d_a, int32_t m
     if (!scope.ok()) return SBLAS_B200_ECUDA;
     std::lock_guard<std::mutex> guard(mat->lock);
     return product_on_stream(mat, d_a, m, lda, d_c, ldc, alpha, beta, static_cast<cudaStream_t>(stream));
+}
+
+int sblas_b200_addmatmat_dev_noalloc(sblas_b200_matrix *mat, const float *d_a, int32_t m, int32_t lda, float *d_c,
+                                     int32_t ldc, float alpha, float beta, void *stream) {
+    int rc = check_product_args(mat, d_a, m, lda, d_c, ldc);
+    if (rc != SBLAS_B200_OK) return rc;
+    DeviceScope scope(mat->device);
+    if (!scope.ok()) return SBLAS_B200_ECUDA;
+    return product_noalloc(mat, d_a, m, lda, d_c, ldc, alpha, beta, static_cast<cudaStream_t>(stream));
 }
 
 int sblas_b200_last_product(const sblas_b200_matrix *mat, sblas_b200_product_info *out) {

@@ -242,6 +242,21 @@ SBLAS_B200_API int sblas_b200_panel_product_host(int32_t trans, int32_t m, int32
  * SBLAS_B200_ECUDA without a device: there is no malloc fallback.
  */
 SBLAS_B200_API int sblas_b200_host_alloc(int64_t bytes, void **ptr);
+/*
+ * Pageable (malloc) buffers: what an unmodified caller of the reference passes
+ * (src/test/blas_test.h:121).  They are staged through the driver (cfg2: 570 us per
+ * call against 157 with the memory above).  With SBLAS_B200_HOST_REGISTER=1 in the
+ * environment (read at every call) a buffer that comes back a SECOND time at the same
+ * address with the same size (>= 64 KiB) is page-locked once with cudaHostRegister
+ * and then takes the overlapped route (cfg2: 179 us).  The registration belongs to
+ * the handle of that call: sblas_b200_free() drops it, at most 4 GiB stay registered
+ * (oldest out first).  Opt-in because of cudaHostRegister's own CONTRACT: a registered
+ * buffer must not be unmapped (free() of a large block) unless
+ * sblas_b200_host_forget(ptr) (NULL = every range) is called first -- a new allocation
+ * at the same address would otherwise be read through the old pages.  For callers that
+ * keep their buffers.  No counterpart in the reference.
+ */
+SBLAS_B200_API int sblas_b200_host_forget(const void *ptr);
 SBLAS_B200_API int sblas_b200_host_free(void *ptr);
 
 /* ---- peer-visible output: reassembly across GPUs without a collective ------ */

@@ -65,6 +65,7 @@ SYMBOLS = {
     "sblas_b200_panel_product_host": (C.c_int, [_i32, _i32, _i32, _i32, _vp, _i32, _vp, _i32, _f32, _vp, _vp, _i32, _vp, _i32]),
     "sblas_b200_host_alloc": (C.c_int, [_i64, _vp]),
     "sblas_b200_host_free": (C.c_int, [_vp]),
+    "sblas_b200_host_forget": (C.c_int, [_vp]),
     "sblas_b200_peer_alloc": (C.c_int, [_i32, _i64, _vp, _vp]),
     "sblas_b200_peer_open": (C.c_int, [_i32, _vp, _i64, _vp]),
     "sblas_b200_peer_close": (C.c_int, [_vp]),

@@ -34,18 +34,16 @@ def _need(x, count, what):
     """Refuse buffers shorter than the library will touch (numpy arrays / torch tensors; raw ints are trusted)."""
     have = None
     if isinstance(x, np.ndarray):
+        if x.dtype != np.float32 or not x.flags.c_contiguous:
+            raise TypeError(f"{what}: expected a C-contiguous float32 array, got {x.dtype}"
+                            f"{'' if x.flags.c_contiguous else ', not contiguous'}")
         have = x.size
     elif hasattr(x, "numel"):
+        if str(getattr(x, "dtype", "torch.float32")) != "torch.float32" or not x.is_contiguous():
+            raise TypeError(f"{what}: expected a contiguous float32 tensor, got {x.dtype}")
         have = x.numel()
     if have is not None and have < count:
         raise ValueError(f"{what} holds {have} elements, the call needs {count}")
-
-
-def _f32c(a):
-    a = np.asarray(a)
-    if a.dtype != np.float32 or not a.flags.c_contiguous:
-        raise TypeError("expected a C-contiguous float32 array")
-    return a
 
 
 class _PinnedBlock:

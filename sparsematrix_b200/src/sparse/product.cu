@@ -483,8 +483,9 @@ static int check_product_args(const sblas_b200_matrix *mat, const float *a, int3
     if (m == 0 || mat->n == 0) return SBLAS_B200_OK;
     if (!c) return fail(SBLAS_B200_EINVAL, "c is null");
     if (!a && mat->k) return fail(SBLAS_B200_EINVAL, "a is null");
-    if (ldc < mat->n) return fail(SBLAS_B200_EINVAL, "ldc %d < n %d", ldc, mat->n);
-    if (lda < mat->k) return fail(SBLAS_B200_EINVAL, "lda %d < k %d", lda, mat->k);
+    // a single dense row never uses its leading dimension (the reference ignores lda / ldc for m == 1)
+    if (m > 1 && ldc < mat->n) return fail(SBLAS_B200_EINVAL, "ldc %d < n %d", ldc, mat->n);
+    if (m > 1 && lda < mat->k) return fail(SBLAS_B200_EINVAL, "lda %d < k %d", lda, mat->k);
     return SBLAS_B200_OK;
 }
 
@@ -832,6 +833,7 @@ int sblas_b200_addmatmat_dev(sblas_b200_matrix *mat, const float *d_a, int32_t m
                              float alpha, float beta, void *stream) {
     int rc = check_product_args(mat, d_a, m, lda, d_c, ldc);
     if (rc != SBLAS_B200_OK) return rc;
+    if (m == 1) { lda = std::max(lda, mat->k); ldc = std::max(ldc, mat->n); }     // unused for one row; keeps the copies' pitches valid
     DeviceScope scope(mat->device);
     if (!scope.ok()) return SBLAS_B200_ECUDA;
     std::lock_guard<std::mutex> guard(mat->lock);
@@ -842,6 +844,7 @@ int sblas_b200_addmatmat_dev_noalloc(sblas_b200_matrix *mat, const float *d_a, i
                                      int32_t ldc, float alpha, float beta, void *stream) {
     int rc = check_product_args(mat, d_a, m, lda, d_c, ldc);
     if (rc != SBLAS_B200_OK) return rc;
+    if (m == 1) { lda = std::max(lda, mat->k); ldc = std::max(ldc, mat->n); }     // unused for one row; keeps the copies' pitches valid
     DeviceScope scope(mat->device);
     if (!scope.ok()) return SBLAS_B200_ECUDA;
     return product_noalloc(mat, d_a, m, lda, d_c, ldc, alpha, beta, static_cast<cudaStream_t>(stream));
@@ -892,6 +895,7 @@ int sblas_b200_addmatmat_host(sblas_b200_matrix *mat, const float *a, int32_t m,
                               float alpha, float beta) {
     int rc = check_product_args(mat, a, m, lda, c, ldc);
     if (rc != SBLAS_B200_OK) return rc;
+    if (m == 1) { lda = std::max(lda, mat->k); ldc = std::max(ldc, mat->n); }     // unused for one row; keeps the copies' pitches valid
     if (m == 0 || mat->n == 0) return SBLAS_B200_OK;
     DeviceScope scope(mat->device);
     if (!scope.ok()) return SBLAS_B200_ECUDA;
@@ -906,6 +910,10 @@ int sblas_b200_addmatmat_host(sblas_b200_matrix *mat, const float *a, int32_t m,
     }
     rc = ensure_buffer(&mat->d_host_c, &mat->host_c_bytes, (size_t)m * n * 4);
     if (rc != SBLAS_B200_OK) return rc;
+    if (need_a) {                                       // pageable buffers seen before get registered (pinned_memory.cu)
+        note_host_buffer(mat, a, ((size_t)(m - 1) * lda + k) * 4);
+        note_host_buffer(mat, c, ((size_t)(m - 1) * ldc + n) * 4);
+    }
     float *c_mapped = need_a ? mapped_pointer(c) : nullptr;
     if (c_mapped && m == 1 && (size_t)(k + n) * 4 <= ((size_t)256 << 10)) {
         static const bool direct = [] { const char *e = getenv("SBLAS_B200_HOST_DIRECT"); return !(e && *e == '0'); }();   // A/B switch

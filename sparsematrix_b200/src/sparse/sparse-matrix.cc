@@ -32,6 +32,19 @@ SBLAS_TMPL void SBLAS_CLS::Destroy() {
     rows_ = cols_ = 0;
 }
 
+SBLAS_TMPL SBLAS_CLS &SBLAS_CLS::operator=(const SBLAS_CLS &oth) {
+    if (this == &oth) return *this;
+    device::Evict(this);                            // the registered device matrix holds the OLD contents
+    pos_index_ = oth.pos_index_;
+    val_index_ = oth.val_index_;
+    val_table_ = oth.val_table_;
+    block_bounds_ = oth.block_bounds_;
+    block_index_bounds_ = oth.block_index_bounds_;
+    rows_ = oth.rows_;
+    cols_ = oth.cols_;
+    return *this;
+}
+
 // CopyForm on the device (src/utils/copyform.cu) for inputs large enough to pay for the trip:
 // fills the members with exactly the bytes the scan below produces and registers the device
 // matrix built from the device-resident streams, so the first AddMatMat uploads nothing.

@@ -54,6 +54,13 @@ public:
         CopyForm(density_matrix, rows, cols, stride, vals, val_table_size, trans);
     }
     ~SparseMatrix() { Destroy(); }
+    // Copies take the compressed members only.  The device copy is registered per object address
+    // (src/utils/device_registry.h): an assigned-to object drops its own -- it would describe the old
+    // contents -- and uploads again on its next AddMatMat.  Member functions: no effect on layout.
+    SparseMatrix(const SparseMatrix &oth)
+        : pos_index_(oth.pos_index_), val_index_(oth.val_index_), val_table_(oth.val_table_), block_bounds_(oth.block_bounds_),
+          block_index_bounds_(oth.block_index_bounds_), rows_(oth.rows_), cols_(oth.cols_) {}
+    SparseMatrix &operator=(const SparseMatrix &oth);
 
     // Clears the compressed members and drops the device copy.
     void Destroy();

@@ -31,6 +31,28 @@ static int run_case(int m, int n, int k, double density, float alpha, float beta
     return bad;
 }
 
+// Copy assignment after a product: `a` already has a device copy of its old contents registered under its
+// address; `a = b` must drop it, so that the next AddMatMat multiplies by b's matrix (the reference class is
+// correct under assignment, its implicit operator= copies the vectors).  A copy-constructed object too.
+static int run_assignment_case() {
+    const int T = 255, n = 300, k = 270, m = 5;
+    std::vector<float> table = uniform_matrix(T, 901);
+    std::vector<uint8_t> ia = index_matrix(n, k, 0.10, T, 902), ib = index_matrix(n, k, 0.15, T, 903);
+    Matrix A(ia.data(), n, k, k, table.data(), T, sblas::SblasTrans), B(ib.data(), n, k, k, table.data(), T, sblas::SblasTrans);
+    std::vector<float> x = uniform_matrix((size_t)m * k, 904), c0 = uniform_matrix((size_t)m * n, 905);
+    std::vector<float> ca = c0, cb = c0, cc = c0, cd = c0;
+    A.AddMatMat(x.data(), m, k, ca.data(), n, 1.3f, 2.0f);                 // registers A's device copy
+    B.AddMatMat(x.data(), m, k, cb.data(), n, 1.3f, 2.0f);
+    A = B;
+    A.AddMatMat(x.data(), m, k, cc.data(), n, 1.3f, 2.0f);                 // must be B's product
+    Matrix D(B);
+    D.AddMatMat(x.data(), m, k, cd.data(), n, 1.3f, 2.0f);
+    const int bad = memcmp(cc.data(), cb.data(), cb.size() * 4) != 0 || memcmp(cd.data(), cb.data(), cb.size() * 4) != 0 ||
+                    memcmp(ca.data(), cb.data(), cb.size() * 4) == 0 || !(A == B);
+    printf("%-4s assignment / copy construction after a product use the new contents\n", bad ? "FAIL" : "ok");
+    return bad;
+}
+
 int main(int argc, char **argv) {
     int failures = 0;
     if (argc >= 5) {
@@ -45,6 +67,7 @@ int main(int argc, char **argv) {
         }
         failures += run_case(1, 4096, 4096, 0.01, 1.0f, 1.0f, 0, 0, 11);      // BASELINE.json configs[0]
         failures += run_case(128, 4096, 4096, 0.10, 1.0f, 1.0f, 0, 0, 12);    // BASELINE.json configs[1]
+        failures += run_assignment_case();
     }
     printf(failures ? "Parity Test fail... (%d case(s))\n" : "Parity Test success...\n", failures);
     return failures ? 1 : 0;

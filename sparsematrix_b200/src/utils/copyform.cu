@@ -226,7 +226,8 @@ int sblas_b200_copyform_begin(const uint8_t *codes, int32_t rows, int32_t cols, 
     job->npanels = npanels; job->chunks_per_panel = cpp;
     CfScratch sc;
     auto bail = [&](int rc) { destroy_job(job); *out = nullptr; return rc; };
-    const size_t dense_bytes = (size_t)rows * stride;
+    // what the reference's scan touches (sparse-matrix.cc:33-54): the last row ends after `cols` elements, not `stride`
+    const size_t dense_bytes = (size_t)(rows - 1) * stride + cols;
     cudaError_t e = cudaMalloc((void **)&sc.codes, dense_bytes);
     if (e == cudaSuccess) e = cudaMemcpy(sc.codes, codes, dense_bytes, cudaMemcpyDefault);
     if (e == cudaSuccess) e = cudaMalloc((void **)&sc.last, (size_t)nchunks * 4);

@@ -732,6 +732,7 @@ int sblas_b200_partition_csr(const int32_t *row_ptr, int32_t n, int32_t parts, i
 int sblas_b200_free(sblas_b200_matrix *mat) {
     if (!mat) return SBLAS_B200_OK;
     DeviceScope scope(mat->device);
+    forget_host_buffers(mat, nullptr);                      // caller buffers this handle's host calls had registered
     release(mat);
     return SBLAS_B200_OK;
 }

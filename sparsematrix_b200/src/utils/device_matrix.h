@@ -198,6 +198,9 @@ int run_spmv_blocked(sblas_b200_matrix *mat, const float *x, float *y, float alp
 // records the dominant kernel of the running product: name, bytes of the device format per non-zero, and the bytes per
 // launch that do not scale with nnz besides X and C (row pointers, segment pointers, ...)
 void note_product(sblas_b200_matrix *mat, const char *kernel, int m, double bytes_per_nnz, int64_t index_bytes);
+// src/utils/pinned_memory.cu: registration cache of pageable caller buffers (second sighting of (address, size) -> cudaHostRegister)
+void note_host_buffer(const void *owner, const void *ptr, size_t bytes);
+void forget_host_buffers(const void *owner, const void *ptr);      // ptr != null: that range; else everything `owner` registered (null: all)
 // src/sparse/product.cu
 int product_on_stream(sblas_b200_matrix *mat, const float *d_a, int32_t m, int32_t lda, float *d_c, int32_t ldc,
                       float alpha, float beta, cudaStream_t stream);

@@ -13,11 +13,14 @@ namespace sblas {
 namespace device {
 
 namespace {
-std::mutex g_lock;
+// Both are heap objects that are never destroyed: a SparseMatrix with static storage duration may run its
+// destructor (-> Evict) after the function-local statics of this file would have been torn down.
+std::mutex &g_lock = *new std::mutex;
 // (owner, device ordinal) -> handle
 std::map<std::pair<const void *, int>, sblas_b200_matrix *> &table() {
-    static std::map<std::pair<const void *, int>, sblas_b200_matrix *> t;
-    return t;
+    static std::map<std::pair<const void *, int>, sblas_b200_matrix *> *t =
+        new std::map<std::pair<const void *, int>, sblas_b200_matrix *>;
+    return *t;
 }
 }  // namespace
 

@@ -231,7 +231,13 @@ def test_bad_csr_and_bad_stream_are_rejected():
         sb.DeviceMatrix.upload(pos, cd, tab, 255, [[0, 0]], [[0, 3]], 2, 256)    # rows = 2 but pos reaches row 2
     with pytest.raises(sb.SblasError):
         d = sb.DeviceMatrix.upload(np.array([1], np.uint8), np.array([0], np.uint8), tab, 255, [[0, 0]], [[0, 1]], 4, 8)
-        d.addmatmat_host(np.zeros(4, np.float32), 1, 2, np.zeros(8, np.float32), 8, 1.0, 1.0)   # lda < k
+        d.addmatmat_host(np.zeros(8, np.float32), 2, 2, np.zeros(16, np.float32), 8, 1.0, 1.0)   # lda < k with m > 1
+    # a single dense row never uses lda / ldc (the reference ignores them for m == 1): accepted
+    d = sb.DeviceMatrix.upload(np.array([1], np.uint8), np.array([0], np.uint8), tab, 255, [[0, 0]], [[0, 1]], 4, 8)
+    y = d.addmatmat_host(np.ones(4, np.float32), 1, 0, np.zeros(8, np.float32), 0, 1.0, 1.0)
+    assert y[1] == tab[0] and not y[[0, 2, 3, 4, 5, 6, 7]].any()
+    with pytest.raises(TypeError):
+        d.addmatmat_host(np.ones(4, np.float64), 1, 4, np.zeros(8, np.float32), 8, 1.0, 1.0)      # dtype is checked
 
 
 # ------------------------------------------------------------------ device-pointer entry point + slabs
@@ -529,6 +535,81 @@ def test_device_copyform_edge_cases_and_host_class_route():
         assert np.array_equal(np.asarray(x), np.asarray(y))
     assert_bits_equal(D.AddMatMat(a, 5, k, c0.copy(), n, 1.3, 2.0), H.AddMatMat(a, 5, k, c0.copy(), n, 1.3, 2.0), "device-built vs host-built object")
     assert np.array_equal(D.CopyTo(k, sb.SparseMatrix.Trans), H.CopyTo(k, sb.SparseMatrix.Trans))    # S^T is n x k: stride >= k
+
+
+def test_pageable_buffers_seen_twice_are_registered_and_give_the_same_bits():
+    """The registration cache of the host entry point (pinned_memory.cu): the first call with malloc'ed buffers is staged,
+    the second registers them, later ones take the overlapped route -- every call must produce the first call's bits."""
+    import os
+    n, k, m = 2048, 1024, 96                        # a: 384 KiB, c: 768 KiB (both above the 64 KiB floor)
+    old_env = os.environ.get("SBLAS_B200_HOST_REGISTER")
+    os.environ["SBLAS_B200_HOST_REGISTER"] = "1"     # opt-in, read per call
+    try:
+        _registered_pageable_case(n, k, m)
+    finally:
+        sb.lib().sblas_b200_host_forget(None)
+        if old_env is None: os.environ.pop("SBLAS_B200_HOST_REGISTER", None)
+        else: os.environ["SBLAS_B200_HOST_REGISTER"] = old_env
+
+
+def _registered_pageable_case(n, k, m):
+    codes = gen.codes_bernoulli(n, k, 0.05, seed=51)
+    tab = gen.codebook(255, 1)
+    s = O.copyform(codes, n, k, k, tab, 255, True)
+    dev = upload(s)
+    a = gen.dense_uniform((m, k), 52)
+    c0 = gen.dense_uniform((m, n), 53)
+    c = np.empty_like(c0)
+    outs = []
+    for call in range(4):
+        c[...] = c0
+        dev.addmatmat_host(a, m, k, c, n, 1.3, 2.0)
+        outs.append(c.copy())
+    for call in range(1, 4):
+        assert_bits_equal(outs[call], outs[0], f"call {call + 1} with the same pageable buffers")
+    check_values(outs[3], s, a, m, k, c0, n, 1.3, 2.0, "registered pageable buffers")
+    # a strided C (ldc > n) through the same mechanism; padding untouched
+    ldc = n + 8
+    c2 = gen.dense_uniform((m, ldc), 54)
+    c2_0 = c2.copy()
+    for call in range(3):
+        c2[...] = c2_0
+        dev.addmatmat_host(a, m, k, c2, ldc, 1.0, 1.0)
+    check_values(c2, s, a, m, k, c2_0, ldc, 1.0, 1.0, "registered strided C")
+    assert sb.lib().sblas_b200_host_forget(a.ctypes.data_as(C.c_void_p)) == 0
+    c[...] = c0
+    dev.addmatmat_host(a, m, k, c, n, 1.3, 2.0)                     # a is pageable again, c still registered
+    assert_bits_equal(c, outs[0], "after host_forget(a)")
+    dev.free()                                                       # drops the remaining registrations
+    assert sb.lib().sblas_b200_host_forget(None) == 0
+
+
+def test_device_copyform_reads_no_byte_past_the_last_row():
+    """A strided view whose last row ends at the end of its allocation: (rows-1)*stride + cols bytes, not rows*stride
+    (ADVICE r01).  The buffer ends flush against a PROT_NONE page, so an over-read faults."""
+    import ctypes
+    import mmap
+    rows, cols, stride, T = 600, 500, 512, 255                 # rows*cols >= 2^18: the host class takes the device route
+    need = (rows - 1) * stride + cols
+    page = mmap.PAGESIZE
+    span = (need + page - 1) // page * page
+    mm = mmap.mmap(-1, span + page)
+    base = ctypes.addressof(ctypes.c_char.from_buffer(mm))
+    libc = ctypes.CDLL(None, use_errno=True)
+    assert libc.mprotect(ctypes.c_void_p(base + span), ctypes.c_size_t(page), 0) == 0        # guard page
+    buf = np.frombuffer(mm, dtype=np.uint8, count=need, offset=span - need)
+    full = np.full((rows, stride), 255, np.uint8)
+    full[:, :cols] = gen.codes_bernoulli(rows, cols, 0.1, seed=41)
+    buf[:] = full.reshape(-1)[:need]
+    tab = gen.codebook(T, 1)
+    want = O.copyform(full, rows, cols, stride, tab, T, False)
+    pos, code, bb, bib, dev = sb.copyform_device(buf, rows, cols, stride, tab, T, False)
+    _assert_same_streams(pos, code, bb, bib, want, "minimal-size strided input")
+    S = sb.SparseMatrix(buf, rows, cols, stride, tab, T, sb.SparseMatrix.NoTrans)
+    p2, c2, _, _, _, _ = S.members()
+    assert np.array_equal(p2, want.pos) and np.array_equal(c2, want.code)
+    del buf, S
+    libc.mprotect(ctypes.c_void_p(base + span), ctypes.c_size_t(page), 3)
 
 
 def test_decode_dense_into_device_memory():

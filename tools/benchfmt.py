@@ -14,7 +14,8 @@ def row(name, d):
         extra = " | sharded-C %.1f us allgather %.1f us balance %.3f ceiling %.2fx" % (
             d["sharded_output"]["ms_per_step"] * 1e3, d["reassembly_allgather_ms"] * 1e3, d["slab_balance"], d["model_scaling_ceiling"])
     if "e2e_pageable" in d:
-        extra += " | pageable %.1f us" % (d["e2e_pageable"]["ms_per_step"] * 1e3)
+        extra += " | pageable %.1f us (registered %.1f)" % (d["e2e_pageable"]["ms_per_step"] * 1e3,
+                                                             d.get("e2e_pageable_registered", {}).get("ms_per_step", float("nan")) * 1e3)
     if "cpu_baseline" in d:
         extra += " | cpu %.2f GF/s (%s)" % (d["cpu_baseline"]["value"], d["cpu_baseline"]["kind"])
     print("%-5s %9.0f GF/s step %8.1f us kern %8.1f us (%s) warm %8.1f us e2e %8.1f us | %s frac %.3f hbm %.3f fp32 %.3f | parity %s %.1e upload %.0f ms%s" % (

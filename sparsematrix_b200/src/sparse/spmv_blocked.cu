@@ -6,15 +6,17 @@
 //
 //   pass 1  persistent CTAs walk the slot stream; the x tile of the current column block (cbw floats)
 //           sits in shared memory, the codebook * alpha is replicated per lane (conflict-free look-up):
-//           p[slot] = fl(x_s[lcol] * tab[code])          3 B read + 4 B written per entry, no global gather
+//           p[slot] = fl(x_s[lcol] * tab[code]), and inside a quad of slots the products of one row's run are
+//           added left to right (the format keeps a run inside a quad): 3 B read + 4 B written per slot,
+//           no global gather
 //   pass 2  one warp per row sub-block (rs rows, sums in shared memory) walks its sub-segments in column
-//           block order -- the entries of one row arrive in column order, the order of the reference's
-//           accumulation -- four neighbouring slots per lane (8 + 16 byte loads), and adds each run of equal
-//           rows to the row's sum: 6 B read per entry.  No CTA barrier anywhere: the warps of a CTA own
-//           disjoint rows.
-// Products and sums are separately rounded like the reference's generic build (no FMA).  A run that spans
-// lanes is added in phases, lane after lane (fixed order: results are run-to-run identical).
-// HBM traffic: 13 B per entry + x + y, against 5 B per entry and one L2 sector per entry for the row kernels.
+//           block order, four neighbouring slots per lane (8 + 16 byte loads), and adds every slot that closes
+//           a run to its row's sum: 6 B read per slot.  Within one 128-slot step no two lanes hold the same row
+//           (a row closes one run per segment) -- except for the quads of a run longer than a quad, which carry a
+//           flag and are added one lane after the other.  No CTA barrier anywhere: the warps of a CTA own disjoint rows.
+// Products and sums are separately rounded like the reference's generic build (no FMA); a row's terms are added
+// run by run in column order, the terms of a run first among themselves: fixed order, run-to-run identical.
+// HBM traffic: 13 B per slot + x + y, against 5 B per entry and one L2 sector per entry for the row kernels.
 #include <stdlib.h>
 
 #include <algorithm>
@@ -31,7 +33,7 @@ constexpr int kP2Warps = 16;
 template <int U>
 __global__ void __launch_bounds__(kP1Threads, 1)
 spmv_blocked_pass1_kernel(const uint2 *__restrict__ lcol4, const uint32_t *__restrict__ code4,
-                          const int32_t *__restrict__ cb_start, int ncb, int cbw, const float *__restrict__ x, int k,
+                          const int32_t *__restrict__ cb_start, int cb_lo, int cb_hi, int cbw, const float *__restrict__ x, int k,
                           const float *__restrict__ table, int T, float alpha, float4 *__restrict__ prod4, int x_vec) {
     extern __shared__ __align__(16) float smem[];
     float *tab_s = smem;                                    // [256][32]: entry c of lane l at c * 32 + l
@@ -41,12 +43,13 @@ spmv_blocked_pass1_kernel(const uint2 *__restrict__ lcol4, const uint32_t *__res
         const int c = i >> 5;
         tab_s[i] = c < T ? table[c] * alpha : 0.0f;         // val_table[code] * alpha (kernel.cc:791)
     }
-    const int total_q = cb_start[ncb] >> 2;                 // quads of slots
+    // this launch covers the column blocks [cb_lo, cb_hi): quads [q_lo, q_hi), a contiguous share per CTA
+    const int q_lo = cb_start[cb_lo] >> 2, total_q = (cb_start[cb_hi] >> 2) - q_lo;
     constexpr int kStep = kP1Threads * U;
-    const int q_first = (int)(((int64_t)total_q * blockIdx.x / gridDim.x) / kStep * kStep);
-    const int q_end = blockIdx.x + 1 == gridDim.x ? total_q
-                                                  : (int)(((int64_t)total_q * (blockIdx.x + 1) / gridDim.x) / kStep * kStep);
-    int q = q_first, cb = 0;
+    const int q_first = q_lo + (int)(((int64_t)total_q * blockIdx.x / gridDim.x) / kStep * kStep);
+    const int q_end = q_lo + (blockIdx.x + 1 == gridDim.x ? total_q
+                                                          : (int)(((int64_t)total_q * (blockIdx.x + 1) / gridDim.x) / kStep * kStep));
+    int q = q_first, cb = cb_lo;
     const float *tab_l = tab_s + lane;
     while (q < q_end) {
         while ((cb_start[cb + 1] >> 2) <= q) ++cb;          // the block slot q lies in (empty blocks skipped)
@@ -70,11 +73,14 @@ spmv_blocked_pass1_kernel(const uint2 *__restrict__ lcol4, const uint32_t *__res
 #pragma unroll
             for (int u = 0; u < U; ++u) {
                 if (qq + u * kP1Threads < stop) {
-                    float4 p;
-                    p.x = x_s[lc[u].x & 0xffffu] * tab_l[(cd[u] << 5) & 0x1fe0u];
-                    p.y = x_s[lc[u].x >> 16] * tab_l[(cd[u] >> 3) & 0x1fe0u];
-                    p.z = x_s[lc[u].y & 0xffffu] * tab_l[(cd[u] >> 11) & 0x1fe0u];
-                    p.w = x_s[lc[u].y >> 16] * tab_l[(cd[u] >> 19) & 0x1fe0u];
+                    float4 p;                               // bit 15 of a local column: the slot continues its left neighbour's run
+                    p.x = x_s[lc[u].x & 0x7fffu] * tab_l[(cd[u] << 5) & 0x1fe0u];
+                    p.y = x_s[(lc[u].x >> 16) & 0x7fffu] * tab_l[(cd[u] >> 3) & 0x1fe0u];
+                    p.z = x_s[lc[u].y & 0x7fffu] * tab_l[(cd[u] >> 11) & 0x1fe0u];
+                    p.w = x_s[(lc[u].y >> 16) & 0x7fffu] * tab_l[(cd[u] >> 19) & 0x1fe0u];
+                    if (lc[u].x & 0x80000000u) p.y = p.x + p.y;
+                    if (lc[u].y & 0x00008000u) p.z = p.y + p.z;
+                    if (lc[u].y & 0x80000000u) p.w = p.z + p.w;
                     __stcs(prod4 + qq + u * kP1Threads, p);
                 }
             }
@@ -87,17 +93,18 @@ __device__ __forceinline__ void red_add_f32(float *p, float v) {
     asm volatile("red.global.add.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
 }
 
-// One step of a warp is a chunk of 32 quads (128 slots): lane l holds four neighbouring slots, i.e. rows r0 <= r1 <= r2 <= r3
-// (0xffff = padding) and their products.  Inside the lane the products of equal rows are added left to right (column order).
-// Only one kind of run crosses lanes: a lane's first run may continue the previous lane's last one.  Such a head run is held
-// back and added in a later phase -- phase d for a lane d lanes away from where the run began -- so that no two lanes ever
-// update the same row at once and every sum is formed in a fixed order.  D = chunks a warp keeps in flight.
+// One step of a warp is a chunk of 32 quads (128 slots) of one sub-segment: lane l holds four neighbouring slots -- their
+// row fields (0xffff: nothing to add; bit 14: closes a run that began in an earlier quad) and their pass-1 sums.  Slots
+// without bit 14 name pairwise different rows across the whole chunk, so the lanes add them at once, slot index after slot
+// index; the flagged ones (at most one per lane) follow, one lane after the other in lane = column order.
+// D = chunks a warp keeps in flight.
 template <int D>
 __global__ void __launch_bounds__(32 * kP2Warps, 2)
 spmv_blocked_pass2_kernel(const uint2 *__restrict__ lrow4, const float4 *__restrict__ prod4,
-                          const int32_t *__restrict__ seg_ptr, int ncb, int nsub, int rs, int n, float *__restrict__ y,
-                          float beta, int red) {
+                          const int32_t *__restrict__ seg_ptr, int cb_lo, int ncb, int nsub, int rs, int n, float *__restrict__ y,
+                          float beta, int red, int abl) {      // column blocks [cb_lo, ncb)
     extern __shared__ float y_all[];                        // [warps][rs]
+    float sink = 0.0f;                                      // experiments (abl != 0): where the sums go instead of shared memory
     const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int sub = blockIdx.x * kP2Warps + w;
     if (sub >= nsub) return;                                // warps are independent: no CTA barrier below
@@ -109,90 +116,110 @@ spmv_blocked_pass2_kernel(const uint2 *__restrict__ lrow4, const float4 *__restr
     const size_t stride = (size_t)nsub + 1;
     const int32_t *sp = seg_ptr + sub;                      // (block cb, this sub-block) at sp[cb * stride]
     int pb_next = 0, pe_next = 0;                           // in quads
-    if (lane < ncb) { pb_next = sp[lane * stride] >> 2; pe_next = sp[lane * stride + 1] >> 2; }
-    for (int cb0 = 0; cb0 < ncb; cb0 += 32) {               // a window of 32 column blocks, one per lane
+    if (cb_lo + lane < ncb) { pb_next = sp[(size_t)(cb_lo + lane) * stride] >> 2; pe_next = sp[(size_t)(cb_lo + lane) * stride + 1] >> 2; }
+    // One chunk into the sums.  The fields without bit 14 name pairwise different rows across the chunk (also inside a
+    // lane): four independent read-modify-writes per lane, reads first.
+    auto add_chunk = [&](const uint2 r, const float4 v) {
+        if (abl) { sink += v.x + v.y + v.z + v.w + __uint_as_float(r.x ^ r.y); return; }   // timing experiment
+        const uint32_t late = ((r.x & ~(r.x >> 1)) | (r.y & ~(r.y >> 1))) & 0x40004000u;
+        const unsigned late_lanes = __ballot_sync(0xffffffffu, late != 0u);
+        const bool a0 = !(r.x & 0x0000c000u), a1 = !(r.x & 0xc0000000u), a2 = !(r.y & 0x0000c000u), a3 = !(r.y & 0xc0000000u);
+        float *p0 = y_s + (r.x & 0x3fffu), *p1 = y_s + ((r.x >> 16) & 0x3fffu), *p2 = y_s + (r.y & 0x3fffu),
+              *p3 = y_s + ((r.y >> 16) & 0x3fffu);
+        float t0 = 0.f, t1 = 0.f, t2 = 0.f, t3 = 0.f;
+        if (a0) t0 = *p0;
+        if (a1) t1 = *p1;
+        if (a2) t2 = *p2;
+        if (a3) t3 = *p3;
+        t0 += v.x; t1 += v.y; t2 += v.z; t3 += v.w;
+        if (a0) *p0 = t0;
+        if (a1) *p1 = t1;
+        if (a2) *p2 = t2;
+        if (a3) *p3 = t3;
+        if (late_lanes) {                                   // uniform; rare: a row with more than four entries in one column block
+            uint32_t lr = 0xffffu;                          // the lane's flagged field, if any (at most one per quad)
+            float lv = 0.0f;
+            if ((r.x & 0x0000c000u) == 0x00004000u) { lr = r.x & 0xffffu; lv = v.x; }
+            if ((r.x & 0xc0000000u) == 0x40000000u) { lr = r.x >> 16; lv = v.y; }
+            if ((r.y & 0x0000c000u) == 0x00004000u) { lr = r.y & 0xffffu; lv = v.z; }
+            if ((r.y & 0xc0000000u) == 0x40000000u) { lr = r.y >> 16; lv = v.w; }
+            for (unsigned todo = late_lanes; todo; todo &= todo - 1) {
+                __syncwarp();
+                if (lane == __ffs(todo) - 1) y_s[lr & 0x3fffu] += lv;
+            }
+        }
+        __syncwarp();                                       // the next chunk may name a row of this one
+    };
+    for (int cb0 = cb_lo; cb0 < ncb; cb0 += 32) {           // a window of 32 column blocks, one per lane
         const int pb = pb_next, pe = pe_next;
         pb_next = pe_next = 0;
         if (cb0 + 32 + lane < ncb) {                        // the next window's pointers travel while this one is added
             pb_next = sp[(size_t)(cb0 + 32 + lane) * stride] >> 2;
             pe_next = sp[(size_t)(cb0 + 32 + lane) * stride + 1] >> 2;
         }
-        const int nc = (pe - pb + 31) >> 5;                 // chunks of this lane's sub-segment
-        int cs = nc;                                        // inclusive scan: chunks up to and including this lane
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, cs, o);
-            if (lane >= o) cs += t;
-        }
-        const int total_chunks = __shfl_sync(0xffffffffu, cs, 31);
-        // chunk j of the window belongs to the first lane whose inclusive count exceeds j
-        auto issue = [&](int j, uint2 &r, float4 &v) {
+        const int ncw = min(32, ncb - cb0);
+        // the first 32 quads of column block cb0 + c (nearly always the whole sub-segment)
+        auto fetch = [&](int c, uint2 &r, float4 &v) {
             r = make_uint2(0xffffffffu, 0xffffffffu);
             v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (j < total_chunks) {                         // uniform
-                const int l = __ffs(__ballot_sync(0xffffffffu, cs > j)) - 1;
-                const int b = __shfl_sync(0xffffffffu, pb, l), e = __shfl_sync(0xffffffffu, pe, l);
-                const int first = __shfl_sync(0xffffffffu, cs - nc, l);
-                const int q = b + ((j - first) << 5) + lane;
-                if (q < e) { r = __ldcs(lrow4 + q); v = __ldcs(prod4 + q); }
+            if (c < ncw) {                                  // uniform
+                const int q = __shfl_sync(0xffffffffu, pb, c) + lane;
+                if (q < __shfl_sync(0xffffffffu, pe, c)) { r = __ldcs(lrow4 + q); v = __ldcs(prod4 + q); }
             }
         };
-        uint2 rq[D];
-        float4 vq[D];
+        // D sub-segments per step: their loads go out together, then they are added one after the other.  (A load issued
+        // while older ones are awaited buys nothing here: the wait is for every load of the warp that is in flight.)
+        for (int c0 = 0; c0 < ncw; c0 += D) {
+            uint2 rq[D];
+            float4 vq[D];
 #pragma unroll
-        for (int d = 0; d < D; ++d) issue(d, rq[d], vq[d]);
-        for (int j0 = 0; j0 < total_chunks; j0 += D) {
+            for (int d = 0; d < D; ++d) fetch(c0 + d, rq[d], vq[d]);
 #pragma unroll
             for (int d = 0; d < D; ++d) {
-                if (j0 + d < total_chunks) {                // uniform
-                    const uint2 r = rq[d];
-                    const float4 v = vq[d];
-                    issue(j0 + d + D, rq[d], vq[d]);
-                    const uint32_t r0 = r.x & 0xffffu, r1 = r.x >> 16, r2 = r.y & 0xffffu, r3 = r.y >> 16;
-                    const bool e1 = r1 == r0, e2 = r2 == r1, e3 = r3 == r2;
-                    const float s0 = v.x;
-                    const float s1 = e1 ? s0 + v.y : v.y;
-                    const float s2 = e2 ? s1 + v.z : v.z;
-                    const float s3 = e3 ? s2 + v.w : v.w;
-                    const uint32_t prev3 = __shfl_up_sync(0xffffffffu, r3, 1);
-                    const bool cont = lane > 0 && r0 == prev3 && r0 != 0xffffu;      // my head run began in an earlier lane
-                    const int h = !e1 ? 0 : (!e2 ? 1 : (!e3 ? 2 : 3));               // slot that closes the head run
-                    const unsigned cmask = __ballot_sync(0xffffffffu, cont);
-                    // phase 0: every run that closes inside this lane, except a held-back head run
-                    if (!e1 && r0 != 0xffffu && !cont) y_s[r0] += s0;
-                    if (!e2 && r1 != 0xffffu && !(cont && h == 1)) y_s[r1] += s1;
-                    if (!e3 && r2 != 0xffffu && !(cont && h == 2)) y_s[r2] += s2;
-                    if (r3 != 0xffffu && !(cont && h == 3)) y_s[r3] += s3;
-                    if (cmask) {                            // uniform
-                        const float hs = h == 0 ? s0 : (h == 1 ? s1 : (h == 2 ? s2 : s3));
-                        // lanes whose whole quad continues a run pass it on: my distance = 1 + such lanes directly below me
-                        const unsigned fmask = __ballot_sync(0xffffffffu, cont && h == 3);
-                        const unsigned below = lane ? (fmask << (32 - lane)) : 0u;
-                        const int dist = cont ? 1 + __clz(~below) : 0;
-                        for (int p = 1;; ++p) {
-                            __syncwarp();
-                            if (dist == p) y_s[r0] += hs;
-                            if (!__any_sync(0xffffffffu, dist > p)) break;
-                        }
+                const int c = c0 + d;
+                if (c < ncw) {                              // uniform
+                    add_chunk(rq[d], vq[d]);
+                    const int e = __shfl_sync(0xffffffffu, pe, c);
+                    for (int q0 = __shfl_sync(0xffffffffu, pb, c) + 32; q0 < e; q0 += 32) {   // a sub-segment of more than 128 slots
+                        uint2 r2 = make_uint2(0xffffffffu, 0xffffffffu);
+                        float4 v2 = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (q0 + lane < e) { r2 = __ldcs(lrow4 + q0 + lane); v2 = __ldcs(prod4 + q0 + lane); }
+                        add_chunk(r2, v2);
                     }
-                    __syncwarp();                           // the next chunk may continue a row of this one
                 }
             }
         }
     }
     __syncwarp();
+    if (abl && sink == 12345.678f) y_s[0] = sink;
     const int row0 = sub * rs;
-    for (int i = lane; i < rs && row0 + i < n; i += 32) {
-        const float s = y_s[i];
-        const bool nothing = __float_as_uint(s) == 0x80000000u;       // no entry (or only -0 products): the sum changes nothing
-        if (red) {                                          // y in a peer GPU's memory, beta == 1: add at the owner, never read
-            if (!nothing) red_add_f32(y + row0 + i, s);
-            continue;
+    const int rows = min(rs, n - row0);
+    constexpr int EU = 8;                                   // rows per lane and step: their y values travel together
+    for (int i0 = lane; i0 < rows; i0 += 32 * EU) {
+        float s[EU], c0[EU];
+#pragma unroll
+        for (int u = 0; u < EU; ++u) {
+            const int i = i0 + 32 * u;
+            s[u] = i < rows ? y_s[i] : negz;
+            // no entry (or only -0 products): the sum changes nothing; y is read only where it will be rewritten
+            const bool nothing = __float_as_uint(s[u]) == 0x80000000u;
+            c0[u] = 0.0f;
+            if (i < rows && !red && !(nothing && beta == 1.0f)) c0[u] = y[row0 + i];
         }
-        if (nothing && beta == 1.0f) continue;              // column without entries, no scale: untouched
-        float c0 = y[row0 + i];
-        if (beta != 1.0f) c0 *= beta;
-        y[row0 + i] = c0 + s;
+#pragma unroll
+        for (int u = 0; u < EU; ++u) {
+            const int i = i0 + 32 * u;
+            if (i >= rows) continue;
+            const bool nothing = __float_as_uint(s[u]) == 0x80000000u;
+            if (red) {                                      // y in a peer GPU's memory, beta == 1: add at the owner, never read
+                if (!nothing) red_add_f32(y + row0 + i, s[u]);
+                continue;
+            }
+            if (nothing && beta == 1.0f) continue;          // column without entries, no scale: untouched
+            float c = c0[u];
+            if (beta != 1.0f) c *= beta;
+            y[row0 + i] = c + s[u];
+        }
     }
 }
 
@@ -209,6 +236,7 @@ int run_spmv_blocked(sblas_b200_matrix *mat, const float *x, float *y, float alp
     if (!configured) {
         SB_CUDA(cudaFuncSetAttribute(spmv_blocked_pass1_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         SB_CUDA(cudaFuncSetAttribute(spmv_blocked_pass2_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kP2Warps * kBlockedMaxRows * 4));
+        SB_CUDA(cudaFuncSetAttribute(spmv_blocked_pass2_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kP2Warps * kBlockedMaxRows * 4));
         configured = true;
     }
     struct Timer {                                           // event pair around both passes when profiling
@@ -223,14 +251,25 @@ int run_spmv_blocked(sblas_b200_matrix *mat, const float *x, float *y, float alp
                  (13.0 * (double)bf.entries + 5.0 * (double)(mat->nnz - bf.entries)) / (double)mat->nnz,
                  (int64_t)bf.ncb * (bf.nsub + 1) * 4);
     const int x_vec = (reinterpret_cast<uintptr_t>(x) & 15) == 0 && (bf.cbw & 3) == 0;
-    const int grid1 = (int)std::max<int64_t>(1, std::min<int64_t>(sms, bf.total / (4 * kP1Threads * 4)));
-    SB_LAUNCH(spmv_blocked_pass1_kernel<4>, grid1, kP1Threads, smem1, stream, reinterpret_cast<const uint2 *>(bf.d_lcol),
-              reinterpret_cast<const uint32_t *>(bf.d_code), bf.d_cb_start, bf.ncb, bf.cbw, x, mat->k, mat->d_table, mat->T,
-              alpha, reinterpret_cast<float4 *>(bf.d_prod), x_vec);
+    // experiment switches (timing only; results are wrong with them): SBLAS_B200_BLK_ONLY = 1 | 2 runs one pass,
+    // SBLAS_B200_BLK_ABL = 1 drops pass 2's shared-memory updates; SBLAS_B200_BLK_D = 2 | 4 sub-segments per pass-2 step
+    // (profiles/r02_blocked_spmv.md)
+    const char *e_only = getenv("SBLAS_B200_BLK_ONLY"), *e_abl = getenv("SBLAS_B200_BLK_ABL");
+    const int only = e_only ? atoi(e_only) : 0, abl = e_abl ? atoi(e_abl) : 0;
     const int grid2 = (bf.nsub + kP2Warps - 1) / kP2Warps;
-    SB_LAUNCH(spmv_blocked_pass2_kernel<4>, grid2, 32 * kP2Warps, smem2, stream, reinterpret_cast<const uint2 *>(bf.d_lrow),
-              reinterpret_cast<const float4 *>(bf.d_prod), bf.d_seg_ptr, bf.ncb,
-              bf.nsub, bf.rs, mat->n, y, beta, red ? 1 : 0);
+    const char *e_d = getenv("SBLAS_B200_BLK_D");
+    const int depth = e_d ? atoi(e_d) : 2;
+    const int grid1 = (int)std::max<int64_t>(1, std::min<int64_t>(sms, bf.total / (4 * kP1Threads * 4)));
+    if (only != 2)
+        SB_LAUNCH(spmv_blocked_pass1_kernel<4>, grid1, kP1Threads, smem1, stream, reinterpret_cast<const uint2 *>(bf.d_lcol),
+                  reinterpret_cast<const uint32_t *>(bf.d_code), bf.d_cb_start, 0, bf.ncb, bf.cbw, x, mat->k, mat->d_table, mat->T,
+                  alpha, reinterpret_cast<float4 *>(bf.d_prod), x_vec);
+#define SB_P2(DD) SB_LAUNCH(spmv_blocked_pass2_kernel<DD>, grid2, 32 * kP2Warps, smem2, stream, reinterpret_cast<const uint2 *>(bf.d_lrow), \
+              reinterpret_cast<const float4 *>(bf.d_prod), bf.d_seg_ptr, 0, bf.ncb, bf.nsub, bf.rs, mat->n, y, beta, red ? 1 : 0, abl)
+    if (only != 1) {
+        if (depth == 4) SB_P2(4); else SB_P2(2);
+    }
+#undef SB_P2
     SB_CHECK_LAUNCH();
     return SBLAS_B200_OK;
 }

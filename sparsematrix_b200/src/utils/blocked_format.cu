@@ -5,7 +5,9 @@
 // kernel (power-law case: 0.20 of the HBM roofline).  This layout buys locality with a second copy
 // of the entries: sorted by (column block, row, column), two-byte local column and row numbers, so
 // that one pass can keep the block's x tile in shared memory and a second pass can add the products
-// of a row range out of a plain stream.  Inside a row the order stays column-ascending, which is
+// of a row range out of a plain stream.  The entries of one row inside one column block (a run) sit
+// in one quad of slots -- padded if need be -- so that pass 1 can add them and pass 2 sees a row once
+// per (block, sub-block) segment; longer runs fill whole quads and are flagged.  Inside a row the order stays column-ascending, which is
 // the order the reference adds the terms of one output element in (kernel.cc:780-796).
 //
 // Three kernels over the CSR of W (nothing is sorted on the host):
@@ -28,14 +30,33 @@ constexpr int kBlkWarps = 8;            // warps (= row sub-blocks) per CTA of t
 constexpr int kMaxColBlocks = 256;      // shared-memory counters per warp
 constexpr int kSlotAlign = 32;          // a column block starts on a multiple of this many slots (128 B of products)
 
+// Slot rules shared by the counting and the scattering kernel.  A RUN = the entries of one row inside one column block
+// (neighbours in the row, columns ascending).  Pass 1 adds the products of a run inside a quad of slots and pass 2 adds
+// only the slot that closes it, so a run must not straddle a quad unless it is longer than a quad:
+//   run of L <= 4 slots: placed at the cursor, after padding to the next quad if it would not fit the current one;
+//   run of L  > 4 slots: starts on a quad, fills whole quads; every quad closes with a partial sum of the row.
+__device__ __forceinline__ int run_start(int cursor, int len) {
+    if (len > 4 || (cursor & 3) + len > 4) cursor = (cursor + 3) & ~3;
+    return cursor;
+}
+
+// first index in [lo, hi) whose column is >= bound (columns ascend inside a row)
+__device__ __forceinline__ int lower_bound_col(const int32_t *__restrict__ col, int lo, int hi, int64_t bound) {
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if ((int64_t)col[mid] < bound) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
 __global__ void __launch_bounds__(32 * kBlkWarps)
 blocked_count_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col, int n, int rs, int nsub, int cbw,
-                     int ncb, int long_threshold, int32_t *__restrict__ cnt, int32_t *__restrict__ cb_total,
+                     int ncb, int long_threshold, int seg_align, int32_t *__restrict__ cnt, int32_t *__restrict__ cb_total,
                      unsigned long long *__restrict__ stats /* [0] runs, [1] entries */) {
-    __shared__ int32_t hist[kBlkWarps][kMaxColBlocks];
+    __shared__ int32_t cursor[kBlkWarps][kMaxColBlocks];
     const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int sub = blockIdx.x * kBlkWarps + w;
-    for (int i = lane; i < kMaxColBlocks; i += 32) hist[w][i] = 0;
+    for (int i = lane; i < kMaxColBlocks; i += 32) cursor[w][i] = 0;
     __syncwarp();
     if (sub >= nsub) return;
     const int r0 = sub * rs, r1 = min(n, r0 + rs);
@@ -43,21 +64,22 @@ blocked_count_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restr
     for (int row = r0; row < r1; ++row) {
         const int s = row_ptr[row], e = row_ptr[row + 1];
         if (e - s > long_threshold) continue;
-        int carry = -1;                                     // column block of the row's previous entry
         for (int base = s; base < e; base += 32) {
             const int i = base + lane;
             const bool in = i < e;
             const int cb = in ? col[i] / cbw : -1;
-            if (in) { atomicAdd(&hist[w][cb], 1); ++ents; }
-            int prev = __shfl_up_sync(0xffffffffu, cb, 1);
-            if (lane == 0) prev = carry;
-            if (in && cb != prev) ++runs;
-            carry = __shfl_sync(0xffffffffu, cb, 31);
+            const bool head = in && (i == s || col[i - 1] / cbw != cb);    // the run's first entry (one run per row and block)
+            if (in) ++ents;
+            if (head) {
+                const int len = lower_bound_col(col, i + 1, e, (int64_t)(cb + 1) * cbw) - i;
+                cursor[w][cb] = run_start(cursor[w][cb], len) + len;
+                ++runs;
+            }
         }
+        __syncwarp();                                       // the next row's runs see this row's cursors
     }
-    __syncwarp();
     for (int i = lane; i < ncb; i += 32) {
-        const int32_t c = (hist[w][i] + 3) & ~3;            // a sub-segment starts on a quad of slots (vector loads)
+        const int32_t c = (cursor[w][i] + seg_align - 1) & ~(seg_align - 1);   // a sub-segment is a whole number of quads (vector loads), or of 128-byte lines
         cnt[(size_t)i * nsub + sub] = c;
         if (c) atomicAdd(&cb_total[i], c);
     }
@@ -113,11 +135,15 @@ blocked_ptr_kernel(const int32_t *__restrict__ cnt, const int32_t *__restrict__ 
     if (threadIdx.x == 0) out[nsub] = carry;
 }
 
+// lcol bit 15: the slot continues the run of the slot before it in the same quad (pass 1 adds the two products).
+// lrow: 0xffff = nothing to add from this slot (padding, or a slot inside a run); otherwise the row inside the sub-block
+// (bits 0..13) of the run this slot closes, bit 14 set when the run began in an earlier quad (pass 2 then adds it in turn).
 __global__ void __launch_bounds__(32 * kBlkWarps)
 blocked_scatter_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col, const uint8_t *__restrict__ code,
                        int n, int rs, int nsub, int cbw, int ncb, int long_threshold, const int32_t *__restrict__ seg_ptr,
                        uint16_t *__restrict__ lcol, uint16_t *__restrict__ lrow, uint8_t *__restrict__ ocode) {
     __shared__ int32_t cursor[kBlkWarps][kMaxColBlocks];
+    __shared__ int32_t start_of[kBlkWarps][kMaxColBlocks];  // first slot of the current row's run in each block
     const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int sub = blockIdx.x * kBlkWarps + w;
     if (sub >= nsub) return;
@@ -131,21 +157,29 @@ blocked_scatter_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__res
             const int i = base + lane;
             const bool in = i < e;
             const int c = in ? col[i] : 0;
-            const int cb = in ? c / cbw : kMaxColBlocks + lane;
-            // lanes of one column block, in lane (= column) order -> stable rank
-            const unsigned peers = __match_any_sync(0xffffffffu, cb);
-            const int rank = __popc(peers & ((1u << lane) - 1u));
-            int off = 0;
-            if (in) off = cursor[w][cb];
-            __syncwarp();
-            if (in && lane == 31 - __clz(peers)) cursor[w][cb] = off + __popc(peers);
+            const int cb = in ? c / cbw : 0;
+            const bool head = in && (i == s || col[i - 1] / cbw != cb);
+            if (head) {
+                const int len = lower_bound_col(col, i + 1, e, (int64_t)(cb + 1) * cbw) - i;
+                const int st = run_start(cursor[w][cb], len);   // slots are relative to nothing: seg_ptr is quad aligned
+                start_of[w][cb] = st;
+                cursor[w][cb] = st + len;
+            }
             __syncwarp();
             if (in) {
-                const int d = off + rank;
-                lcol[d] = (uint16_t)(c - cb * cbw);
-                lrow[d] = (uint16_t)(row - r0);
+                const int first = head ? i : lower_bound_col(col, s, i, (int64_t)cb * cbw);   // index of the run's first entry
+                const int st = start_of[w][cb];
+                const int d = st + (i - first);
+                const bool last = i + 1 == e || col[i + 1] / cbw != cb;
+                uint16_t lc = (uint16_t)(c - cb * cbw);
+                if (i > first && (d & 3) != 0) lc |= 0x8000u;
+                uint16_t lr = 0xffffu;
+                if (last || (d & 3) == 3) lr = (uint16_t)((row - r0) | (((d >> 2) != (st >> 2)) ? 0x4000 : 0));
+                lcol[d] = lc;
+                lrow[d] = lr;
                 ocode[d] = code[i];
             }
+            __syncwarp();
         }
     }
 }
@@ -158,7 +192,9 @@ int env_int(const char *name, int fallback) {
 }  // namespace
 
 // When the layout pays: x far beyond the L1s (>= 2^21 columns = 8 MB) and enough entries to fill
-// the machine with row sub-blocks of useful size (>= 2^25).  SBLAS_B200_SPMV_BLOCKED = 0 | 1 forces
+// the machine with row sub-blocks of useful size (>= 2^26: every warp of pass 2 walks all column blocks one after
+// the other, about a microsecond each, whatever its share of the rows -- a half-size slab of the 2^23-row power-law
+// matrix takes 332 us this way and 305 us with the length-sorted row kernel).  SBLAS_B200_SPMV_BLOCKED = 0 | 1 forces
 // it off / on (tests build it on small matrices; _CBW and _RS then shrink the geometry).
 int build_blocked_format(sblas_b200_matrix *mat) {
     BlockedFormat &bf = mat->blocked;
@@ -166,9 +202,9 @@ int build_blocked_format(sblas_b200_matrix *mat) {
     bf.state = -1;
     const int mode = env_int("SBLAS_B200_SPMV_BLOCKED", -1);
     if (mode == 0 || !mat->csr_sorted || mat->n < 1 || mat->k < 1 || mat->nnz < 1) return SBLAS_B200_OK;
-    if (mode != 1 && (mat->k < (1 << 21) || mat->nnz < ((int64_t)1 << 25))) return SBLAS_B200_OK;
+    if (mode != 1 && (mat->k < (1 << 21) || mat->nnz < ((int64_t)1 << 26))) return SBLAS_B200_OK;
     int cbw = env_int("SBLAS_B200_BLOCKED_CBW", 32768);
-    cbw = std::min(49152, std::max(4, cbw & ~3));
+    cbw = std::min(32768, std::max(4, cbw & ~3));           // 15 bits of local column, bit 15 of lcol is a flag
     const int ncb = (int)(((int64_t)mat->k + cbw - 1) / cbw);
     if (ncb > kMaxColBlocks) return SBLAS_B200_OK;
     int sms = 0;
@@ -195,8 +231,10 @@ int build_blocked_format(sblas_b200_matrix *mat) {
     SB_CUDA(cudaMemset(sc.cb_total, 0, (size_t)ncb * 4));
     SB_CUDA(cudaMemset(sc.stats, 0, 16));
     const int grid = (nsub + kBlkWarps - 1) / kBlkWarps;
+    int seg_align = env_int("SBLAS_B200_BLOCKED_ALIGN", 4);
+    if (seg_align != 4 && seg_align != 8 && seg_align != 16 && seg_align != 32) seg_align = 4;
     SB_LAUNCH(blocked_count_kernel, grid, 32 * kBlkWarps, 0, 0, mat->d_row_ptr, mat->d_col, mat->n, rs, nsub, cbw, ncb,
-              mat->long_threshold, sc.cnt, sc.cb_total, sc.stats);
+              mat->long_threshold, seg_align, sc.cnt, sc.cb_total, sc.stats);
     SB_CHECK_LAUNCH();
     std::vector<int32_t> cb_total(ncb), cb_start(ncb + 1, 0);
     unsigned long long stats[2] = {0, 0};

@@ -417,6 +417,11 @@ static void launch_spmm_gather(const sblas_b200_matrix *mat, const float *xt, in
 
 static int run_spmm(sblas_b200_matrix *mat, const float *d_a, int m, int lda, float *d_c, int ldc, float alpha,
                     float beta, cudaStream_t stream) {
+    // dense enough and m >= 32: the tensor cores (src/sparse/spmm_tc.cu)
+    {
+        const int crc = run_spmm_tc(mat, d_a, m, lda, d_c, ldc, alpha, beta, stream);
+        if (crc <= 0) return crc;                       // done (0) or failed (< 0); 1 = not for this product
+    }
     // large m: X staged through shared memory (src/sparse/spmm_tile.cu) once the tile format exists
     // Small m too, unless the (row, chunk) pieces are nearly empty: measured (profiles/r01c_small_m.md) the tile
     // kernel beats the gather kernel 2-3x at m = 2..16 from ~3 entries per piece, and loses 30 % below that.

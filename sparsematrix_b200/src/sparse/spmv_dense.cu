@@ -177,6 +177,13 @@ spmv_dense_kernel(const uint8_t *__restrict__ dense, int64_t kpad, const int32_t
 }  // namespace
 
 // Build the dense code matrix from the CSR (once per handle, on the stream of the first product that wants it).
+static int build_dense_codes(sblas_b200_matrix *mat, cudaStream_t stream);
+int ensure_dense_codes(sblas_b200_matrix *mat, cudaStream_t stream) {
+    if (mat->dense_state == 1) return SBLAS_B200_OK;
+    if (mat->dense_state < 0) return 1;
+    return build_dense_codes(mat, stream);
+}
+
 static int build_dense_codes(sblas_b200_matrix *mat, cudaStream_t stream) {
     const int64_t kpad = ((int64_t)mat->k + kColsPerWarp - 1) / kColsPerWarp * kColsPerWarp;
     const size_t bytes = (size_t)mat->n * kpad;

@@ -430,6 +430,8 @@ static int alloc_csr(sblas_b200_matrix *mat, const float *table) {
     SB_CUDA(cudaMemset(mat->d_code, 0, padded));
     float h_tab[256];
     for (int t = 0; t < 256; ++t) h_tab[t] = (t < mat->T) ? table[t] : 0.0f;
+    for (int t = 0; t < mat->T; ++t)
+        if (!(h_tab[t] - h_tab[t] == 0.0f)) mat->table_finite = false;      // Inf or NaN in the codebook
     SB_CUDA(cudaMemcpy(mat->d_table, h_tab, sizeof(h_tab), cudaMemcpyHostToDevice));
     mat->format_bytes += ((int64_t)mat->n + 1) * 4 + (int64_t)padded * 5 + 1024;
     return SBLAS_B200_OK;
@@ -443,6 +445,7 @@ static void release(sblas_b200_matrix *mat) {
     for (TileFormat &tf : mat->tile) { cudaFree(tf.d_blocks); cudaFree(tf.d_grp_ptr); cudaFree(tf.d_grp_nq); }
     cudaFree(mat->d_ws); cudaFree(mat->d_partial); cudaFree(mat->d_host_a); cudaFree(mat->d_host_c);
     cudaFree(mat->d_host_p); cudaFree(mat->d_dense_code); cudaFree(mat->d_peer_y);
+    cudaFree(mat->d_tc_ws);
     cudaFree(mat->blocked.d_lcol); cudaFree(mat->blocked.d_lrow); cudaFree(mat->blocked.d_code);
     cudaFree(mat->blocked.d_seg_ptr); cudaFree(mat->blocked.d_cb_start); cudaFree(mat->blocked.d_prod);
     if (mat->stream) cudaStreamDestroy(mat->stream);

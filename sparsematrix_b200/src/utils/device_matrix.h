@@ -162,6 +162,11 @@ struct sblas_b200_matrix {
 
     BlockedFormat blocked;
 
+    // Tensor-core SpMM (src/sparse/spmm_tc.cu): workspace [flag | tile counters | X_hi | X_lo | split-k partial tiles]
+    bool table_finite = true;           // every codebook entry is finite (else the matrix stays off that path)
+    float *d_tc_ws = nullptr;   size_t tc_ws_bytes = 0, tc_head_bytes = 0;
+    uint32_t tc_calls = 0;              // id of the latest product on that path (its non-finite-x flag value)
+
     // sblas_b200_last_product: what the most recent product launched as its dominant kernel
     char last_kernel[64] = "";
     int32_t last_m = 0;
@@ -190,6 +195,11 @@ int run_spmm_tile(sblas_b200_matrix *mat, const float *d_a, int m, int lda, floa
                   float beta, cudaStream_t stream);
 // src/sparse/spmv_dense.cu: 0 = done, 1 = not applicable (use the row kernels), < 0 = error
 int run_spmv_dense(sblas_b200_matrix *mat, const float *x, float *y, float alpha, float beta, cudaStream_t stream);
+// builds the one-byte dense code matrix of W when it does not exist yet: 0 = there, 1 = no room, < 0 = error
+int ensure_dense_codes(sblas_b200_matrix *mat, cudaStream_t stream);
+// src/sparse/spmm_tc.cu: 0 = done, 1 = not applicable (use the CUDA-core kernels), < 0 = error
+int run_spmm_tc(sblas_b200_matrix *mat, const float *d_a, int m, int lda, float *d_c, int ldc, float alpha, float beta,
+                cudaStream_t stream);
 constexpr int kBlockedMaxRows = 1792;   // rows per sub-block at most: 16 warps x 1792 floats = 112 KB, two CTAs per SM
 // src/utils/blocked_format.cu: 0 = built or not applicable (see blocked.state), < 0 = error
 int build_blocked_format(sblas_b200_matrix *mat);

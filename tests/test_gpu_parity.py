@@ -803,16 +803,28 @@ def test_config3_full_size_sampled_rows_and_invariants():
     assert dev.nnz == int((codes != 255).sum())
     a = gen.dense_uniform((m, k), 2); c0 = gen.dense_uniform((m, n), 3)
     got = dev.addmatmat_host(a, m, k, c0.copy(), n, 1.3, 2.0)
+    family = dev.last_product()["kernel"].split("<")[0]
     rows = np.random.default_rng(5).choice(n, 48, replace=False)
     err = _sampled_backward_error(got[:, rows], codes[rows], tab, a, c0[:, rows], 1.3, 2.0)
     assert err <= TOL, err
     # an output element does not depend on how many other A rows are multiplied with it (m-tile
-    # shape, kernel variant) nor on the host route (pinned, sliced copies)
+    # shape, kernel variant) nor on the host route (pinned, sliced copies) -- within one kernel family: the tensor-core
+    # form (chosen here for m = 512) and the tile form (chosen for a 64-row slice) add in different orders
     part = dev.addmatmat_host(a[100:164], 64, k, c0[100:164].copy(), n, 1.3, 2.0)
-    assert_bits_equal(part, got[100:164], "m = 64 slice vs rows 100..163 of the m = 512 product")
+    if dev.last_product()["kernel"].split("<")[0] == family:
+        assert_bits_equal(part, got[100:164], "m = 64 slice vs rows 100..163 of the m = 512 product")
+    else:
+        assert _sampled_backward_error(part[:, rows], codes[rows], tab, a[100:164], c0[100:164][:, rows], 1.3, 2.0) <= TOL
+    part = dev.addmatmat_host(a[20:500], 480, k, c0[20:500].copy(), n, 1.3, 2.0)
+    assert dev.last_product()["kernel"].split("<")[0] == family
+    assert_bits_equal(part, got[20:500], "m = 480 slice vs rows 20..499 of the m = 512 product (same kernel family)")
     pa = torch.from_numpy(a).pin_memory(); pc = torch.from_numpy(c0.copy()).pin_memory()
     dev.addmatmat_host(pa, m, k, pc, n, 1.3, 2.0)
-    assert_bits_equal(pc.numpy(), got, "pinned + sliced host route at full size")
+    assert _sampled_backward_error(pc.numpy()[:, rows], codes[rows], tab, a, c0[:, rows], 1.3, 2.0) <= TOL
+    tile = _with_env("SBLAS_B200_SPMM_TC", "0", lambda: dev.addmatmat_host(a, m, k, c0.copy(), n, 1.3, 2.0))
+    assert dev.last_product()["kernel"].startswith("spmm_tile")
+    _with_env("SBLAS_B200_SPMM_TC", "0", lambda: dev.addmatmat_host(pa, m, k, pc.copy_(torch.from_numpy(c0)), n, 1.3, 2.0))
+    assert_bits_equal(pc.numpy(), tile, "pinned + sliced host route at full size (tile kernels)")
     # row slabs (8 virtual shards) concatenate to the same bits
     pos, code, table, T, bb, bib = S.members()
     splits = sb.partition(bb, bib, n, 8)

@@ -60,6 +60,7 @@ DESCR = {
     "cfg5": "density sweep, large end: SpMV 16384x16384 at 50% sparsity (BASELINE.json configs[4])",
 }
 FP32_PEAK_NOMINAL_TFLOPS = 2 * 128 * 148 * 1.965e9 / 1e12     # CUDA-core FMA peak at max clock
+TF32_PEAK_NOMINAL_TFLOPS = 2250.0 / 2                         # dense TF32 on tcgen05: half the nominal bf16 rate
 L2_NOTE = "GPU arm: L2 flushed before every timed step (256 MiB write); per-step CUDA events summed"
 METRIC = "SpMV/SpMM GFLOP/s (2*nnz*m / time)"
 TOL = 1e-5                                                    # backward error bound of the parity check
@@ -547,10 +548,27 @@ def measure(name, args, cx):
                 "hbm_frac": ach_gbs / hbm_peak, "hbm_frac_of_8tbs": ach_gbs / 8000.0, "fp32_frac": ach_tf / fp32_peak,
                 "t_roof_us": max(t_hbm_us, t_fp32_us), "roof_frac": max(t_hbm_us, t_fp32_us) / kern_us,
                 "kernel_share_of_step": kern_us / (ms_step * 1e3)}
+        if lp["kernel"].startswith("spmm_tc"):
+            # the tensor-core form multiplies the zeros too: what it executes is the dense contraction, three TF32 products per
+            # element pair (hi*hi + hi*lo + lo*hi), on W padded to 128 rows / 512 columns and the m tile padded to its width
+            n_tile = int(lp["kernel"].split("<")[1].split(">")[0])
+            rows_pad, k_pad, m_pad = -(-(hi - lo) // 128) * 128, -(-k // 512) * 512, -(-m // n_tile) * n_tile
+            tc_flops = 3.0 * 2.0 * rows_pad * k_pad * m_pad
+            tc_peak = TF32_PEAK_NOMINAL_TFLOPS
+            tc_ach = tc_flops / (kern_us * 1e-6) / 1e12
+            roof.update({"bound": "tensor", "achieved": tc_ach, "peak": tc_peak, "unit": "TFLOP/s", "frac": tc_ach / tc_peak,
+                         "executed_tf32_flops": tc_flops,
+                         "peak_source": "tensor: nominal dense TF32 = half of the 2250 TFLOP/s bf16 figure (B200_PROFILING.md); "
+                                        "MEASURED_PEAKS.json has cuBLAS bf16 only: %s TFLOP/s burst, i.e. %.0f for TF32; hbm: %s"
+                                        % (cx.bf16_measured, (cx.bf16_measured or 0) / 2, peak_src),
+                         "useful_tflops": flops_k / (kern_us * 1e-6) / 1e12})
         clk = clocks.summary()
         sm_hz = (clk.get("sm_mhz") or 1965.0) * 1e6
         # what actually bounds the kernel on the chip
-        if lp["kernel"].startswith("spmm_tile"):
+        if lp["kernel"].startswith("spmm_tc"):
+            roof["onchip"] = {"limiter": "tensor pipe (ncu sm__pipe_tc_cycles_active 86 % on cfg3, profiles/r02_cfg3_full.txt); "
+                                         "the CUDA-core form of this product is capped at 25 % of the fp32 peak by the shared-memory pipe"}
+        elif lp["kernel"].startswith("spmm_tile"):
             wavefronts = nnz_local * ((m + 31) // 32)                   # 4*m B of X per non-zero through a 128 B/clk/SM pipe
             t_smem_us = wavefronts / (148 * sm_hz) * 1e6
             roof["onchip"] = {"limiter": "shared-memory pipe (one 128 B wavefront per clock per SM)", "x_wavefronts": int(wavefronts),
@@ -655,6 +673,11 @@ def run_ours(args):
     cx.dev = torch.device("cuda", local_rank)
     cx.flush = torch.empty(256 << 20, dtype=torch.uint8, device=cx.dev)       # > 126 MB L2
     cx.stream = torch.cuda.current_stream()
+    cx.bf16_measured = None
+    try:
+        cx.bf16_measured = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops"])
+    except Exception:
+        pass
     try:
         cx.fp32_peak_tflops = sb.measure_fp32_peak(local_rank)
     except Exception:

@@ -635,6 +635,8 @@ static int host_slice_rows(const sblas_b200_matrix *mat, int m) {
     static const int env_rows = [] { const char *e = getenv("SBLAS_B200_HOST_SLICE_ROWS"); return e ? atoi(e) : -1; }();
     int rows = env_rows;
     if (rows < 0) {
+        // (slices of 256 rows, whole tiles of the tensor-core form, were measured on config 3: 1865 us per call against
+        //  1696 us with 64-row slices through the tile kernel -- the finer slices overlap PCIe better)
         // a slice is at least one m-tile of the SpMM kernel (64 rows) and carries enough bytes to be
         // worth an extra round of launches (>= 4 MB of A); measured on config 3 (profiles/r01_e2e.md)
         rows = 64;

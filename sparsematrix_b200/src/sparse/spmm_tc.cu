@@ -469,16 +469,13 @@ int launch_tc(sblas_b200_matrix *mat, const float *xh, const float *xl, int nkb,
 
 }  // namespace
 
-// 0 = done, 1 = not applicable (the caller runs the CUDA-core kernels), < 0 = error.
-// SBLAS_B200_SPMM_TC = 0 never | 1 whenever possible (read per call: tests flip it).
-int run_spmm_tc(sblas_b200_matrix *mat, const float *d_a, int m, int lda, float *d_c, int ldc, float alpha, float beta,
-                cudaStream_t stream) {
+// The tile width (64 | 128 | 256) the tensor-core form would use for an m-row product of this matrix, 0 when the CUDA-core
+// kernels are expected to be faster or the form does not apply.  *ksplit_out = shares of k.
+static int tc_plan(const sblas_b200_matrix *mat, int m, float alpha, int *ksplit_out) {
     const char *env = getenv("SBLAS_B200_SPMM_TC");
     const int mode = (env && *env) ? atoi(env) : -1;
-    if (mode == 0 || mat->dense_state < 0 || !mat->csr_sorted || !mat->table_finite || !isfinite(alpha)) return 1;
-    if (mat->n < 1 || mat->k < 1 || m < 2) return 1;
-    // C in a peer GPU's memory (sblas_b200_peer_open) and beta == 1: the epilogue adds with reductions at the owner's memory
-    const int red = (is_peer_pointer(d_c) && beta == 1.0f) ? 1 : 0;
+    if (mode == 0 || mat->dense_state < 0 || !mat->csr_sorted || !mat->table_finite || !isfinite(alpha)) return 0;
+    if (mat->n < 1 || mat->k < 1 || m < 2) return 0;
     static int sms = 0;
     if (!sms && (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, mat->device) != cudaSuccess || sms <= 0)) sms = 148;
     const int n_tile = m <= 64 ? 64 : (m <= 128 ? 128 : 256);
@@ -494,17 +491,36 @@ int run_spmm_tc(sblas_b200_matrix *mat, const float *d_a, int m, int lda, float 
     const int share = std::min(128, std::max(8, (nkb / 4 + 3) / 4 * 4));
     int ksplit = std::max(1, (nkb + share - 1) / share);
     if (const char *e = getenv("SBLAS_B200_TC_KSPLIT")) ksplit = std::max(1, std::min(nkb / 4, atoi(e)));
+    *ksplit_out = ksplit;
     if (mode != 1) {
         // Which form is faster?  Measured models, microseconds (profiles/r02_spmm_tc.md): the tile kernel moves one 128-byte
         // shared-memory wavefront per non-zero and 32 dense columns at 58 % of the pipe's rate; a tensor-core CTA spends
         // 0.42 / 0.56 / 0.92 us per 32-column step of k at N = 64 / 128 / 256, CTAs run in waves of one per SM.
-        if (m < 32) return 1;
+        if (m < 32) return 0;
         const double t_tile = 12.0 + (double)mat->nnz * ((m + 31) / 32) / 1.69e5;
         const double t_step = n_tile == 64 ? 0.42 : (n_tile == 128 ? 0.56 : 0.92);
         const int64_t waves = ((int64_t)tiles * ksplit + sms - 1) / sms;
         const double t_tc = 24.0 + (double)waves * ((nkb + ksplit - 1) / ksplit) * t_step + (ksplit > 1 ? 8.0 : 0.0);
-        if (t_tc > 0.9 * t_tile) return 1;
+        if (t_tc > 0.9 * t_tile) return 0;
     }
+    return n_tile;
+}
+
+// 0 = done, 1 = not applicable (the caller runs the CUDA-core kernels), < 0 = error.
+// SBLAS_B200_SPMM_TC = 0 never | 1 whenever possible (read per call: tests flip it).
+int run_spmm_tc(sblas_b200_matrix *mat, const float *d_a, int m, int lda, float *d_c, int ldc, float alpha, float beta,
+                cudaStream_t stream) {
+    int ksplit = 1;
+    const int n_tile = tc_plan(mat, m, alpha, &ksplit);
+    if (!n_tile) return 1;
+    // C in a peer GPU's memory (sblas_b200_peer_open) and beta == 1: the epilogue adds with reductions at the owner's memory
+    const int red = (is_peer_pointer(d_c) && beta == 1.0f) ? 1 : 0;
+    static int sms = 0;
+    if (!sms && (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, mat->device) != cudaSuccess || sms <= 0)) sms = 148;
+    const int mtiles = (m + n_tile - 1) / n_tile;
+    const int64_t kpad = ((int64_t)mat->k + 511) / 512 * 512;
+    const int nkb = (int)(kpad / kTcBK);
+    const int tiles = ((mat->n + kTcM - 1) / kTcM) * mtiles;
     cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
     if (cudaStreamIsCapturing(stream, &cap) != cudaSuccess) { cudaGetLastError(); cap = cudaStreamCaptureStatusNone; }
     const bool capturing = cap != cudaStreamCaptureStatusNone;
@@ -514,22 +530,19 @@ int run_spmm_tc(sblas_b200_matrix *mat, const float *d_a, int m, int lda, float 
         if (rc != SBLAS_B200_OK) return rc;                     // 1: no room for the code matrix
     }
     if (mat->dense_kpad != kpad) return fail(SBLAS_B200_ECUDA, "dense code matrix: padded width %lld, expected %lld", (long long)mat->dense_kpad, (long long)kpad);
-    // workspace: [flag + pad | counters | X_hi | X_lo | partial tiles]
+    // workspace: [flag + pad | tile counters | X_hi | X_lo | partial tiles].  The head keeps the largest size any product of
+    // this handle needed (at least 64 KB), so that the counters of a product with many tiles never lie where a product
+    // with fewer tiles put its X images; they are zero between products (the last CTA of a tile puts its counter back).
     const size_t x_elems = (size_t)mtiles * nkb * n_tile * kTcBK;
-    const size_t head = 256 + (size_t)tiles * 4;
-    const size_t head_pad = (head + 1023) / 1024 * 1024;
+    const size_t head_need = (256 + (size_t)tiles * 4 + 1023) / 1024 * 1024;
+    const size_t head_pad = std::max(std::max(head_need, mat->tc_head_bytes), (size_t)65536);
     const size_t part_elems = ksplit > 1 ? (size_t)tiles * ksplit * n_tile * kTcM : 0;
     const size_t need = head_pad + (2 * x_elems + part_elems) * 4;
-    if (need > mat->tc_ws_bytes) {
-        if (capturing) return 1;
+    if (need > mat->tc_ws_bytes || head_pad != mat->tc_head_bytes) {
+        if (capturing) return 1;                                // no allocation (or re-initialisation) inside a capture
         const int rc = ensure_buffer(&mat->d_tc_ws, &mat->tc_ws_bytes, need);
         if (rc != SBLAS_B200_OK) return rc;
         SB_CUDA(cudaMemsetAsync(mat->d_tc_ws, 0, head_pad, stream));   // flag 0 (call ids start at 1), counters 0
-        mat->tc_head_bytes = 0;
-    }
-    if (head_pad > mat->tc_head_bytes) {                        // more tiles than any product before: their counters start at 0
-        if (capturing) return 1;
-        SB_CUDA(cudaMemsetAsync(mat->d_tc_ws, 0, head_pad, stream));
         mat->tc_head_bytes = head_pad;
     }
     uint8_t *ws = reinterpret_cast<uint8_t *>(mat->d_tc_ws);

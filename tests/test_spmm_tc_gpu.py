@@ -145,3 +145,15 @@ def test_tensor_core_spmm_into_a_registered_peer_range_adds_with_reductions():
         assert dev.last_product()["kernel"].startswith("spmm_tc")
         assert_bits_equal(buf.cpu().numpy(), want.cpu().numpy(), f"peer range beta={beta}")
     dev.free()
+
+
+def test_tensor_core_spmm_products_of_different_shapes_share_one_workspace():
+    """Many tiles (n = 25 600: 200 row blocks) and m going up and down on one handle: the tile counters of the wide product
+    must not lie where the narrow one kept its X images (a layout bug of the first version, caught by bench.py's check)."""
+    n, k = 25600, 256
+    codes = gen.codes_bernoulli(n, k, 0.3, seed=95)
+    s = O.copyform(codes, n, k, k, gen.codebook(255, 1), 255, True)
+    dev = sb.DeviceMatrix.upload(s.pos, s.code, s.table, s.T, s.block_bounds, s.block_index_bounds, s.rows, s.cols)
+    for m in (256, 512, 256, 64, 512):
+        _check(dev, s, m, 1.0, 1.0, seed=m)
+    dev.free()

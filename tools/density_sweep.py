@@ -48,12 +48,18 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--sparsity", type=float, nargs="*", default=[50.0, 75.0, 90.0, 95.0, 99.0, 99.9])
     ap.add_argument("--sizes", type=int, nargs="*", default=None)
+    ap.add_argument("--cpu-big", action="store_true", help="reference CPU and OpenBLAS columns at 16384^2 too (m <= 32 for the reference)")
     args = ap.parse_args()
     dev = torch.device("cuda", 0)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     tab = gen.codebook(255, 1)
-    print("| n=k | sparsity | m | nnz | GPU cold us | GPU warm us | GPU GFLOP/s (cold) | ref CPU ms (1 thread) | CPU GFLOP/s | GPU/CPU | dense OpenBLAS ms (numpy.dot, all cores) |")
-    print("|---|---|---|---|---|---|---|---|---|---|---|")
+    print("| n=k | sparsity | m | nnz | kernel | GPU cold us | GPU warm us | GPU GFLOP/s (cold) | ref CPU ms (1 thread) | CPU GFLOP/s | GPU/CPU | "
+          "dense OpenBLAS ms, 1 thread | dense OpenBLAS ms, all cores |")
+    print("|---|---|---|---|---|---|---|---|---|---|---|---|---|")
+    try:
+        from threadpoolctl import threadpool_limits
+    except Exception:
+        threadpool_limits = None
     sizes = args.sizes or ([4096] + ([16384] if args.big else []))
     for n in sizes:
         for idx, sp in enumerate([50.0, 75.0, 90.0, 95.0, 99.0, 99.9]):
@@ -64,31 +70,41 @@ def main():
             S = sb.SparseMatrix(codes, n, n, n, tab, 255, sb.SparseMatrix.Trans)
             mat = S.device_matrix()
             R = None
-            if n == 4096 and O.have_ref() and not args.no_cpu:
+            cpu_ok = O.have_ref() and not args.no_cpu
+            if cpu_ok and (n == 4096 or args.cpu_big):
                 R = O.RefMatrix()
                 R.CopyForm(codes, n, n, n, tab, 255, True)
+            w = None
+            if cpu_ok and threadpool_limits is not None:     # the reference harness's cross-check: sgemm / sgemv on the dense expansion
+                w = np.where(codes < 255, tab[np.minimum(codes, 254)], np.float32(0)).astype(np.float32)
             for m in args.m:
                 a = gen.dense_uniform((m, n), 2)
                 d_a = torch.from_numpy(a).to(dev)
                 d_c = torch.zeros((m, n), dtype=torch.float32, device=dev)
                 cold, warm = gpu_time(mat, d_a, d_c, m, n, n, flush)
+                kernel = mat.last_product()["kernel"]
                 flops = 2.0 * nnz * m
                 cpu_ms = cpu_gf = ratio = float("nan")
-                if R is not None:
+                if R is not None and (n == 4096 or m <= 32):   # 16384^2 x 256 at 50 % would take a minute per call
                     c = np.zeros((m, n), np.float32)
                     best = 1e9
-                    for _ in range(2):
+                    for _ in range(2 if n == 4096 else 1):
                         t0 = time.perf_counter()
                         R.AddMatMat(a, m, n, c, n, 1.0, 1.0)
                         best = min(best, time.perf_counter() - t0)
                     cpu_ms, cpu_gf, ratio = best * 1e3, flops / best / 1e9, best * 1e6 / cold
-                dense_ms = float("nan")
-                if R is not None:                             # the reference harness's cross-check: sgemm on the dense expansion
-                    w = np.where(codes < 255, tab[np.minimum(codes, 254)], np.float32(0)).astype(np.float32)
-                    np.dot(a, w.T)
-                    t0 = time.perf_counter(); np.dot(a, w.T); dense_ms = (time.perf_counter() - t0) * 1e3
-                print(f"| {n} | {sp}% | {m} | {nnz} | {cold:.1f} | {warm:.1f} | {flops / cold / 1e3:.1f} | {cpu_ms:.2f} | {cpu_gf:.2f} | {ratio:.0f}x | {dense_ms:.2f} |", flush=True)
-            del S, mat
+                dense = [float("nan"), float("nan")]
+                if w is not None:
+                    for which, threads in enumerate((1, os.cpu_count())):
+                        if threads == 1 and n > 4096 and m > 32:
+                            continue                          # 137 GFLOP on one thread: skipped
+                        with threadpool_limits(limits=threads, user_api="blas"):
+                            run = (lambda: np.dot(a, w.T)) if m > 1 else (lambda: np.dot(w, a[0]))
+                            run()
+                            t0 = time.perf_counter(); run(); dense[which] = (time.perf_counter() - t0) * 1e3
+                print(f"| {n} | {sp}% | {m} | {nnz} | {kernel} | {cold:.1f} | {warm:.1f} | {flops / cold / 1e3:.1f} | {cpu_ms:.2f} | {cpu_gf:.2f} | {ratio:.0f}x | "
+                      f"{dense[0]:.2f} | {dense[1]:.2f} |", flush=True)
+            del S, mat, w
 
 
 if __name__ == "__main__":

@@ -108,6 +108,21 @@ SBLAS_B200_API int sblas_b200_upload_slab(const uint8_t *pos_index, const uint8_
                                           int32_t device, sblas_b200_matrix **out);
 
 /*
+ * The same for sblas::SparseMatrix<uint16, uint8, float>: position deltas of TWO bytes
+ * (PosIndex_t = uint16, zero_pad_interval 65535, sparse-matrix.cc:24), so hypersparse
+ * matrices need no fillers below gaps of 65 535 (0.1 % density: 2 bytes + 1 per non-zero
+ * instead of 8.9).  The reference has the code path but never instantiates it
+ * (sparse-matrix.cc:315).  A whole matrix is col_begin = 0,
+ * col_end = cols.  Everything after the upload (device layouts, kernels) is the same.
+ */
+SBLAS_B200_API int sblas_b200_upload_slab16(const uint16_t *pos_index, const uint8_t *val_index, int64_t entries,
+                                            const float *val_table, int32_t valid_table_size,
+                                            const int32_t *block_bounds, const int32_t *block_index_bounds,
+                                            int32_t nblocks, int32_t rows, int32_t cols,
+                                            int32_t col_begin, int32_t col_end,
+                                            int32_t device, sblas_b200_matrix **out);
+
+/*
  * Direct CSR upload of W (n x k) for shapes the panel format cannot hold
  * (e.g. 2^23 rows: SURVEY.md 0.6c).  row_ptr[n+1], col[nnz] ascending inside a
  * row, code[nnz] < T indexing table[T].  Host pointers.

@@ -59,6 +59,30 @@ SBLAS_B200_API int sblas_host_load(sblas_host_matrix *h, const char *path);
 /* The device matrix of this object on the current CUDA device (uploads on first use); NULL on failure. */
 SBLAS_B200_API sblas_b200_matrix *sblas_host_device_matrix(sblas_host_matrix *h);
 
+/*
+ * The same object interface for sblas::SparseMatrix<uint16, uint8, float> -- two-byte position deltas (PosIndex_t = uint16,
+ * reference sparse-matrix.cc:24: zero_pad_interval 65535; the reference never instantiates it, :315).
+ * Hypersparse matrices need no fillers below gaps of 65 535.  CopyForm runs on the host for this instantiation; AddMatMat
+ * uploads through sblas_b200_upload_slab16 and runs the same kernels.
+ */
+typedef struct sblas_host_matrix16 sblas_host_matrix16;
+SBLAS_B200_API sblas_host_matrix16 *sblas_host16_create(void);
+SBLAS_B200_API void sblas_host16_free(sblas_host_matrix16 *h);
+SBLAS_B200_API int sblas_host16_copyform(sblas_host_matrix16 *h, const uint8_t *density_matrix, int32_t rows, int32_t cols,
+                                         int32_t stride, const float *vals, int32_t val_table_size, int32_t trans);
+SBLAS_B200_API void sblas_host16_copyto(sblas_host_matrix16 *h, float *density_matrix, int32_t stride, int32_t trans);
+SBLAS_B200_API int sblas_host16_addmatmat(sblas_host_matrix16 *h, const float *a, int32_t m, int32_t lda, float *c, int32_t ldc,
+                                          float alpha, float beta);
+SBLAS_B200_API int32_t sblas_host16_num_rows(const sblas_host_matrix16 *h);
+SBLAS_B200_API int32_t sblas_host16_num_cols(const sblas_host_matrix16 *h);
+SBLAS_B200_API int64_t sblas_host16_entries(const sblas_host_matrix16 *h);
+SBLAS_B200_API int32_t sblas_host16_nblocks(const sblas_host_matrix16 *h);
+SBLAS_B200_API int32_t sblas_host16_table_size(const sblas_host_matrix16 *h);
+SBLAS_B200_API void sblas_host16_members(const sblas_host_matrix16 *h, const uint16_t **pos_index, const uint8_t **val_index,
+                                         const float **val_table, const int32_t **block_bounds,
+                                         const int32_t **block_index_bounds);
+SBLAS_B200_API sblas_b200_matrix *sblas_host16_device_matrix(sblas_host_matrix16 *h);
+
 #ifdef __cplusplus
 }
 #endif

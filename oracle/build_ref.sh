@@ -23,5 +23,8 @@ g++ $CXXFLAGS -I"$REF/src/sparse" -c "$REF/src/sparse/kernel.cc" -o "$OUT/kernel
 g++ $CXXFLAGS -I"$REF/src/sparse" -c "$REF/src/sparse/sparse-matrix.cc" -o "$OUT/sparse-matrix.o"
 g++ $CXXFLAGS -I"$REF/src/sparse" -c "$HERE/ref_shim.cc" -o "$OUT/ref_shim.o"
 g++ -shared -o "$OUT/libsparsematrix_ref.so" "$OUT/kernel.o" "$OUT/sparse-matrix.o" "$OUT/ref_shim.o"
+# the same sources instantiated with two-byte position deltas (ref_shim16.cc includes them), a library of its own
+g++ $CXXFLAGS -I"$REF/src/sparse" -c "$HERE/ref_shim16.cc" -o "$OUT/ref_shim16.o"
+g++ -shared -o "$OUT/libsparsematrix_ref16.so" "$OUT/ref_shim16.o"
 rm -f "$OUT"/*.o
-echo "built $OUT/libsparsematrix_ref.so"
+echo "built $OUT/libsparsematrix_ref.so $OUT/libsparsematrix_ref16.so"

@@ -50,6 +50,12 @@ def lib():
         L.sbo_copyform.argtypes = [vp, i32, i32, i32, vp, i32, i32, vp, vp, vp, vp, vp, vp, vp, vp]
         L.sbo_copyto.restype = None
         L.sbo_copyto.argtypes = [vp, vp, vp, i32, vp, vp, i32, i32, i32, vp, i32, i32]
+        L.sbo_copyform16.restype = i64
+        L.sbo_copyform16.argtypes = L.sbo_copyform.argtypes
+        L.sbo_copyto16.restype = None
+        L.sbo_copyto16.argtypes = L.sbo_copyto.argtypes
+        L.sbo_stream_to_csr16.restype = i64
+        L.sbo_stream_to_csr16.argtypes = [vp, vp, i32, vp, vp, i32, i32, i32, vp, vp, vp, vp]
         L.sbo_addmatmat.restype = None
         L.sbo_addmatmat.argtypes = [vp, vp, vp, i32, vp, vp, i32, i32, i32, vp, i32, i32, vp, i32, f32, f32]
         L.sbo_addmatmat_f64.restype = None
@@ -138,30 +144,33 @@ class Stream:
 
 # --------------------------------------------------------------------------- C restatement
 
-def copyform(codes, rows, cols, stride, vals, T, trans=False):
-    """oracle CopyForm -> Stream.  codes: uint8 array holding >= rows*stride bytes."""
+def copyform(codes, rows, cols, stride, vals, T, trans=False, wide=False):
+    """oracle CopyForm -> Stream.  codes: uint8 array holding >= rows*stride bytes.
+    wide: two-byte position deltas, the SparseMatrix<uint16, uint8, float> instantiation (Stream.pos is uint16)."""
     L = lib()
+    fn = L.sbo_copyform16 if wide else L.sbo_copyform
     codes = np.ascontiguousarray(codes, dtype=np.uint8).reshape(-1)
     vals = np.ascontiguousarray(vals, dtype=np.float32).reshape(-1)
     nb = C.c_int32(0); sr = C.c_int32(0); sc = C.c_int32(0)
-    n = L.sbo_copyform(_p(codes), rows, cols, stride, _p(vals), T, int(bool(trans)),
-                       None, None, None, None, None, C.byref(nb), C.byref(sr), C.byref(sc))
+    n = fn(_p(codes), rows, cols, stride, _p(vals), T, int(bool(trans)),
+           None, None, None, None, None, C.byref(nb), C.byref(sr), C.byref(sc))
     if n < 0:
         raise ValueError("val_table_size out of range")
-    pos = np.empty(n, np.uint8); code = np.empty(n, np.uint8)
+    pos = np.empty(n, np.uint16 if wide else np.uint8); code = np.empty(n, np.uint8)
     table = np.zeros(T + 1 if T > 0 else 0, np.float32)
     bb = np.zeros((nb.value, 2), np.int32); bib = np.zeros((nb.value, 2), np.int32)
-    L.sbo_copyform(_p(codes), rows, cols, stride, _p(vals), T, int(bool(trans)),
-                   _p(pos), _p(code), _p(table) if T > 0 else None, _p(bb), _p(bib),
-                   C.byref(nb), C.byref(sr), C.byref(sc))
+    fn(_p(codes), rows, cols, stride, _p(vals), T, int(bool(trans)),
+       _p(pos), _p(code), _p(table) if T > 0 else None, _p(bb), _p(bib),
+       C.byref(nb), C.byref(sr), C.byref(sc))
     return Stream(pos, code, table, T, bb, bib, sr.value, sc.value)
 
 
 def copyto(s, stride, trans=False):
     lead = s.cols if trans else s.rows
     dense = np.full((lead, stride), np.float32(1.0), np.float32)  # reference memsets; prove it
-    lib().sbo_copyto(_p(s.pos), _p(s.code), _p(s.table), s.T, _p(s.block_bounds), _p(s.block_index_bounds),
-                     s.nblocks, s.rows, s.cols, _p(dense), stride, int(bool(trans)))
+    fn = lib().sbo_copyto16 if s.pos.dtype == np.uint16 else lib().sbo_copyto
+    fn(_p(s.pos), _p(s.code), _p(s.table), s.T, _p(s.block_bounds), _p(s.block_index_bounds),
+       s.nblocks, s.rows, s.cols, _p(dense), stride, int(bool(trans)))
     return dense
 
 
@@ -185,11 +194,12 @@ def stream_to_csr(s):
     L = lib()
     fill = C.c_int64(0)
     row_ptr = np.zeros(s.cols + 1, np.int32)
-    nnz = L.sbo_stream_to_csr(_p(s.pos), _p(s.code), s.T, _p(s.block_bounds), _p(s.block_index_bounds), s.nblocks,
-                              s.rows, s.cols, _p(row_ptr), None, None, C.byref(fill))
+    fn = L.sbo_stream_to_csr16 if s.pos.dtype == np.uint16 else L.sbo_stream_to_csr
+    nnz = fn(_p(s.pos), _p(s.code), s.T, _p(s.block_bounds), _p(s.block_index_bounds), s.nblocks,
+             s.rows, s.cols, _p(row_ptr), None, None, C.byref(fill))
     col = np.empty(nnz, np.int32); code = np.empty(nnz, np.uint8)
-    L.sbo_stream_to_csr(_p(s.pos), _p(s.code), s.T, _p(s.block_bounds), _p(s.block_index_bounds), s.nblocks,
-                        s.rows, s.cols, _p(row_ptr), _p(col), _p(code), C.byref(fill))
+    fn(_p(s.pos), _p(s.code), s.T, _p(s.block_bounds), _p(s.block_index_bounds), s.nblocks,
+       s.rows, s.cols, _p(row_ptr), _p(col), _p(code), C.byref(fill))
     return row_ptr, col, code, fill.value
 
 
@@ -267,6 +277,80 @@ class RefMatrix:
         pos = np.empty(n, np.uint8); code = np.empty(n, np.uint8); table = np.zeros(tl, np.float32)
         bb = np.zeros((nb, 2), np.int32); bib = np.zeros((nb, 2), np.int32)
         self._R.sref_export(self._h, _p(pos), _p(code), _p(table), _p(bb), _p(bib))
+        return Stream(pos, code, table, max(tl - 1, 0), bb, bib, self.NumRows(), self.NumCols())
+
+
+_REF16_SO = os.path.join(_HERE, "_ref", "libsparsematrix_ref16.so")
+_ref16 = None
+
+
+def have_ref16():
+    return os.path.exists(_REF16_SO)
+
+
+def ref16():
+    global _ref16
+    if _ref16 is None:
+        if not have_ref16():
+            raise RuntimeError("oracle/_ref/libsparsematrix_ref16.so is missing (oracle/build_ref.sh builds it where /root/reference exists)")
+        R = C.CDLL(_REF16_SO)
+        vp = C.c_void_p
+        i32, i64, f32 = C.c_int32, C.c_int64, C.c_float
+        R.sref16_create.restype = vp
+        R.sref16_free.argtypes = [vp]
+        R.sref16_copyform.argtypes = [vp, vp, i32, i32, i32, vp, i32, i32]
+        R.sref16_copyto.argtypes = [vp, vp, i32, i32]
+        R.sref16_addmatmat.argtypes = [vp, vp, i32, i32, vp, i32, f32, f32]
+        for name, res in (("rows", i32), ("cols", i32), ("entries", i64), ("nblocks", i32), ("table_len", i32)):
+            fn = getattr(R, "sref16_" + name)
+            fn.argtypes = [vp]; fn.restype = res
+        R.sref16_export.argtypes = [vp, vp, vp, vp, vp, vp]
+        _ref16 = R
+    return _ref16
+
+
+class Ref16Matrix:
+    """sblas::SparseMatrix<uint16,uint8,float> of the unmodified reference (oracle/ref_shim16.cc): two-byte position deltas."""
+
+    def __init__(self):
+        self._R = ref16()
+        self._h = C.c_void_p(self._R.sref16_create())
+
+    def __del__(self):
+        try:
+            if self._h:
+                self._R.sref16_free(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    def CopyForm(self, codes, rows, cols, stride, vals, T, trans=False):
+        codes = np.ascontiguousarray(codes, dtype=np.uint8).reshape(-1)
+        vals = np.ascontiguousarray(vals, dtype=np.float32).reshape(-1)
+        self._R.sref16_copyform(self._h, _p(codes), rows, cols, stride, _p(vals), T, int(bool(trans)))
+
+    def CopyTo(self, stride, trans=False):
+        lead = self.NumCols() if trans else self.NumRows()
+        dense = np.full((lead, stride), np.float32(1.0), np.float32)
+        self._R.sref16_copyto(self._h, _p(dense), stride, int(bool(trans)))
+        return dense
+
+    def AddMatMat(self, a, m, lda, c, ldc, alpha, beta):
+        assert a.dtype == np.float32 and c.dtype == np.float32
+        self._R.sref16_addmatmat(self._h, _p(a), m, lda, _p(c), ldc, alpha, beta)
+        return c
+
+    def NumRows(self):
+        return self._R.sref16_rows(self._h)
+
+    def NumCols(self):
+        return self._R.sref16_cols(self._h)
+
+    def stream(self):
+        n = self._R.sref16_entries(self._h); nb = self._R.sref16_nblocks(self._h); tl = self._R.sref16_table_len(self._h)
+        pos = np.empty(n, np.uint16); code = np.empty(n, np.uint8); table = np.zeros(tl, np.float32)
+        bb = np.zeros((nb, 2), np.int32); bib = np.zeros((nb, 2), np.int32)
+        self._R.sref16_export(self._h, _p(pos), _p(code), _p(table), _p(bb), _p(bib))
         return Stream(pos, code, table, max(tl - 1, 0), bb, bib, self.NumRows(), self.NumCols())
 
 

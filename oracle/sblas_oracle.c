@@ -51,16 +51,28 @@
  * with buffers.  Returns the number of stream entries (fillers included);
  * *nblocks_out = number of non-empty panels.
  * ------------------------------------------------------------------------- */
-SBO_API int64_t sbo_copyform(const uint8_t *codes, int32_t rows, int32_t cols, int32_t stride,
-                             const float *vals, int32_t T, int32_t trans,
-                             uint8_t *pos, uint8_t *code, float *table /* T+1 */,
+/* position deltas are PosIndex_t: one byte in the reference's only instantiation (sparse-matrix.cc:315), two bytes in
+ * SparseMatrix<uint16, uint8, float> -- the same code paths with zero_pad_interval = 65535 (:24); pb = bytes per delta */
+static inline uint32_t rd_pos(const void *pos, int pb, int64_t i)
+{
+    return pb == 1 ? (uint32_t)((const uint8_t *)pos)[i] : (uint32_t)((const uint16_t *)pos)[i];
+}
+static inline void wr_pos(void *pos, int pb, int64_t i, uint32_t v)
+{
+    if (pb == 1) ((uint8_t *)pos)[i] = (uint8_t)v; else ((uint16_t *)pos)[i] = (uint16_t)v;
+}
+
+static int64_t copyform_impl(const uint8_t *codes, int32_t rows, int32_t cols, int32_t stride,
+                             const float *vals, int32_t T, int32_t trans, int pb,
+                             void *pos, uint8_t *code, float *table /* T+1 */,
                              int32_t *block_bounds /* 2*nblocks: (row_off, col_off) */,
                              int32_t *block_index_bounds /* 2*nblocks: [start, end) */,
                              int32_t *nblocks_out, int32_t *s_rows_out, int32_t *s_cols_out)
 {
     int64_t n_entries = 0;
     int32_t n_blocks = 0;
-    if (T < 0 || T > SBO_MAX_DELTA) return -1;          /* :25 assert */
+    const int32_t max_delta = pb == 1 ? SBO_MAX_DELTA : 65535;   /* :24 zero_pad_interval */
+    if (T < 0 || T > SBO_MAX_DELTA) return -1;          /* :25 assert (codes are one byte in both instantiations) */
     if (T == 0) {                                       /* :26 empty object, rows_/cols_ stay 0 */
         if (nblocks_out) *nblocks_out = 0;
         if (s_rows_out) *s_rows_out = 0;
@@ -84,12 +96,12 @@ SBO_API int64_t sbo_copyform(const uint8_t *codes, int32_t rows, int32_t cols, i
                 if (cd >= T) continue;                  /* :44 */
                 const int32_t lin = r * SBO_PANEL_WIDTH + jj;   /* :41 stride is 256 even in a narrow panel */
                 int32_t d = lin - prev;
-                while (d > SBO_MAX_DELTA) {             /* :46-51 filler */
-                    if (pos) { pos[n_entries] = SBO_MAX_DELTA; code[n_entries] = (uint8_t)T; }
+                while (d > max_delta) {                 /* :46-51 filler */
+                    if (pos) { wr_pos(pos, pb, n_entries, (uint32_t)max_delta); code[n_entries] = (uint8_t)T; }
                     ++n_entries;
-                    d -= SBO_MAX_DELTA;
+                    d -= max_delta;
                 }
-                if (pos) { pos[n_entries] = (uint8_t)d; code[n_entries] = cd; }
+                if (pos) { wr_pos(pos, pb, n_entries, (uint32_t)d); code[n_entries] = cd; }
                 ++n_entries;
                 prev = lin;
             }
@@ -109,13 +121,30 @@ SBO_API int64_t sbo_copyform(const uint8_t *codes, int32_t rows, int32_t cols, i
     return n_entries;
 }
 
+SBO_API int64_t sbo_copyform(const uint8_t *codes, int32_t rows, int32_t cols, int32_t stride,
+                             const float *vals, int32_t T, int32_t trans,
+                             uint8_t *pos, uint8_t *code, float *table, int32_t *block_bounds,
+                             int32_t *block_index_bounds, int32_t *nblocks_out, int32_t *s_rows_out, int32_t *s_cols_out)
+{
+    return copyform_impl(codes, rows, cols, stride, vals, T, trans, 1, pos, code, table, block_bounds, block_index_bounds,
+                         nblocks_out, s_rows_out, s_cols_out);
+}
+SBO_API int64_t sbo_copyform16(const uint8_t *codes, int32_t rows, int32_t cols, int32_t stride,
+                               const float *vals, int32_t T, int32_t trans,
+                               uint16_t *pos, uint8_t *code, float *table, int32_t *block_bounds,
+                               int32_t *block_index_bounds, int32_t *nblocks_out, int32_t *s_rows_out, int32_t *s_cols_out)
+{
+    return copyform_impl(codes, rows, cols, stride, vals, T, trans, 2, pos, code, table, block_bounds, block_index_bounds,
+                         nblocks_out, s_rows_out, s_cols_out);
+}
+
 /* ------------------------------------------------------------------------- *
  * Decode to dense.  Follows sparse-matrix.cc:101-137 (CopyTo).
  *   trans == 0 : dense is s_rows x stride, dense[r*stride + j] = S(r,j)
  *   trans == 1 : dense is s_cols x stride, dense[j*stride + r] = S(r,j)
  * Note the reference clears rows_*stride (resp. cols_*stride) floats first.
  * ------------------------------------------------------------------------- */
-SBO_API void sbo_copyto(const uint8_t *pos, const uint8_t *code, const float *table, int32_t T,
+static void copyto_impl(const void *pos, int pb, const uint8_t *code, const float *table, int32_t T,
                         const int32_t *block_bounds, const int32_t *block_index_bounds, int32_t nblocks,
                         int32_t s_rows, int32_t s_cols, float *dense, int32_t stride, int32_t trans)
 {
@@ -125,13 +154,26 @@ SBO_API void sbo_copyto(const uint8_t *pos, const uint8_t *code, const float *ta
         const int32_t row_off = block_bounds[2 * b], col_off = block_bounds[2 * b + 1];
         int32_t lin = 0;
         for (int32_t e = block_index_bounds[2 * b]; e < block_index_bounds[2 * b + 1]; ++e) {
-            lin += pos[e];                                              /* :116 */
+            lin += (int32_t)rd_pos(pos, pb, e);                         /* :116 */
             if (code[e] == T) continue;                                 /* :117 */
             const int32_t r = row_off + (lin >> SBO_PANEL_SHIFT), j = col_off + (lin & SBO_PANEL_MASK);
             if (trans) dense[(int64_t)j * stride + r] = table[code[e]]; /* :133 */
             else       dense[(int64_t)r * stride + j] = table[code[e]]; /* :119 */
         }
     }
+}
+
+SBO_API void sbo_copyto(const uint8_t *pos, const uint8_t *code, const float *table, int32_t T,
+                        const int32_t *block_bounds, const int32_t *block_index_bounds, int32_t nblocks,
+                        int32_t s_rows, int32_t s_cols, float *dense, int32_t stride, int32_t trans)
+{
+    copyto_impl(pos, 1, code, table, T, block_bounds, block_index_bounds, nblocks, s_rows, s_cols, dense, stride, trans);
+}
+SBO_API void sbo_copyto16(const uint16_t *pos, const uint8_t *code, const float *table, int32_t T,
+                          const int32_t *block_bounds, const int32_t *block_index_bounds, int32_t nblocks,
+                          int32_t s_rows, int32_t s_cols, float *dense, int32_t stride, int32_t trans)
+{
+    copyto_impl(pos, 2, code, table, T, block_bounds, block_index_bounds, nblocks, s_rows, s_cols, dense, stride, trans);
 }
 
 /* ------------------------------------------------------------------------- *
@@ -219,7 +261,7 @@ SBO_API void sbo_addmatmat_f64(const uint8_t *pos, const uint8_t *code, const fl
  * Returns nnz (stored non-zeros, fillers dropped); *fillers_out counts fillers.
  * Call with col == NULL to size.
  * ------------------------------------------------------------------------- */
-SBO_API int64_t sbo_stream_to_csr(const uint8_t *pos, const uint8_t *code, int32_t T,
+static int64_t stream_to_csr_impl(const void *pos, int pb, const uint8_t *code, int32_t T,
                                   const int32_t *block_bounds, const int32_t *block_index_bounds, int32_t nblocks,
                                   int32_t s_rows, int32_t s_cols,
                                   int32_t *row_ptr, int32_t *col, uint8_t *csr_code, int64_t *fillers_out)
@@ -232,7 +274,7 @@ SBO_API int64_t sbo_stream_to_csr(const uint8_t *pos, const uint8_t *code, int32
         const int32_t col_off = block_bounds[2 * b + 1];
         int32_t lin = 0;
         for (int32_t e = block_index_bounds[2 * b]; e < block_index_bounds[2 * b + 1]; ++e) {
-            lin += pos[e];
+            lin += (int32_t)rd_pos(pos, pb, e);
             if (code[e] >= T) { ++fillers; continue; }
             ++cnt[col_off + (lin & SBO_PANEL_MASK)];
             ++nnz;
@@ -252,7 +294,7 @@ SBO_API int64_t sbo_stream_to_csr(const uint8_t *pos, const uint8_t *code, int32
             const int32_t row_off = block_bounds[2 * b], col_off = block_bounds[2 * b + 1];
             int32_t lin = 0;
             for (int32_t e = block_index_bounds[2 * b]; e < block_index_bounds[2 * b + 1]; ++e) {
-                lin += pos[e];
+                lin += (int32_t)rd_pos(pos, pb, e);
                 if (code[e] >= T) continue;
                 const int32_t j = col_off + (lin & SBO_PANEL_MASK);
                 col[cur[j]] = row_off + (lin >> SBO_PANEL_SHIFT);
@@ -264,6 +306,21 @@ SBO_API int64_t sbo_stream_to_csr(const uint8_t *pos, const uint8_t *code, int32
     }
     free(cnt);
     return nnz;
+}
+
+SBO_API int64_t sbo_stream_to_csr(const uint8_t *pos, const uint8_t *code, int32_t T,
+                                  const int32_t *block_bounds, const int32_t *block_index_bounds, int32_t nblocks,
+                                  int32_t s_rows, int32_t s_cols,
+                                  int32_t *row_ptr, int32_t *col, uint8_t *csr_code, int64_t *fillers_out)
+{
+    return stream_to_csr_impl(pos, 1, code, T, block_bounds, block_index_bounds, nblocks, s_rows, s_cols, row_ptr, col, csr_code, fillers_out);
+}
+SBO_API int64_t sbo_stream_to_csr16(const uint16_t *pos, const uint8_t *code, int32_t T,
+                                    const int32_t *block_bounds, const int32_t *block_index_bounds, int32_t nblocks,
+                                    int32_t s_rows, int32_t s_cols,
+                                    int32_t *row_ptr, int32_t *col, uint8_t *csr_code, int64_t *fillers_out)
+{
+    return stream_to_csr_impl(pos, 2, code, T, block_bounds, block_index_bounds, nblocks, s_rows, s_cols, row_ptr, col, csr_code, fillers_out);
 }
 
 /* ------------------------------------------------------------------------- *

@@ -43,6 +43,7 @@ SYMBOLS = {
     "sblas_b200_launch_count": (_i64, []),
     "sblas_b200_upload": (C.c_int, [_vp, _vp, _i64, _vp, _i32, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
     "sblas_b200_upload_slab": (C.c_int, [_vp, _vp, _i64, _vp, _i32, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
+    "sblas_b200_upload_slab16": (C.c_int, [_vp, _vp, _i64, _vp, _i32, _vp, _vp, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
     "sblas_b200_upload_csr": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
     "sblas_b200_partition": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp]),
     "sblas_b200_partition_csr": (C.c_int, [_vp, _i32, _i32, _i32, _vp]),
@@ -88,6 +89,18 @@ SYMBOLS = {
     "sblas_host_table_size": (_i32, [_vp]),
     "sblas_host_members": (None, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "sblas_host_device_matrix": (_vp, [_vp]),
+    "sblas_host16_create": (_vp, []),
+    "sblas_host16_free": (None, [_vp]),
+    "sblas_host16_copyform": (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _i32, _i32]),
+    "sblas_host16_copyto": (None, [_vp, _vp, _i32, _i32]),
+    "sblas_host16_addmatmat": (C.c_int, [_vp, _vp, _i32, _i32, _vp, _i32, _f32, _f32]),
+    "sblas_host16_num_rows": (_i32, [_vp]),
+    "sblas_host16_num_cols": (_i32, [_vp]),
+    "sblas_host16_entries": (_i64, [_vp]),
+    "sblas_host16_nblocks": (_i32, [_vp]),
+    "sblas_host16_table_size": (_i32, [_vp]),
+    "sblas_host16_members": (None, [_vp, _vp, _vp, _vp, _vp, _vp]),
+    "sblas_host16_device_matrix": (_vp, [_vp]),
     "sblas_host_save": (C.c_int, [_vp, C.c_char_p]),
     "sblas_host_load": (C.c_int, [_vp, C.c_char_p]),
 }

@@ -348,3 +348,80 @@ class SparseMatrix:
     def upload_slab(self, col_begin, col_end, device=0):
         pos, code, table, T, bb, bib = self.members()
         return DeviceMatrix.upload(pos, code, table, T, bb, bib, self.NumRows(), self.NumCols(), device, col_begin, col_end)
+
+
+class SparseMatrix16:
+    """sblas::SparseMatrix<uint16,uint8,float> of this build: two-byte position deltas (no fillers below gaps of 65 535).
+    The reference has the code path (sparse-matrix.cc:24) but never instantiates it (:315)."""
+
+    NoTrans, Trans = 0, 1
+
+    def __init__(self, density_matrix=None, rows=0, cols=0, stride=0, vals=None, val_table_size=0, trans=0):
+        self._L = _capi.lib()
+        self._h = C.c_void_p(self._L.sblas_host16_create())
+        if not self._h:
+            raise MemoryError("sblas_host16_create")
+        if density_matrix is not None:
+            self.CopyForm(density_matrix, rows, cols, stride, vals, val_table_size, trans)
+
+    def __del__(self):
+        try:
+            if self._h:
+                self._L.sblas_host16_free(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    def CopyForm(self, density_matrix, rows, cols, stride, vals, val_table_size, trans=0):
+        dm = np.ascontiguousarray(density_matrix, np.uint8).reshape(-1)
+        if dm.shape[0] < (rows - 1) * stride + cols and rows > 0:
+            raise ValueError("density_matrix smaller than rows x stride")
+        vals = np.ascontiguousarray(vals, np.float32).reshape(-1)
+        if vals.shape[0] < val_table_size:
+            raise ValueError("vals shorter than val_table_size")
+        if self._L.sblas_host16_copyform(self._h, _ptr(dm), rows, cols, stride, _ptr(vals), val_table_size, int(trans)) != _capi.OK:
+            raise ValueError("val_table_size outside [0, 255]")
+
+    def CopyTo(self, stride, trans=0):
+        lead = self.NumCols() if trans else self.NumRows()
+        minor = self.NumRows() if trans else self.NumCols()
+        if stride < minor:
+            raise ValueError(f"stride {stride} < {minor}: the dense output would be overrun")
+        dense = np.full((lead, stride), np.float32(1.0), np.float32)
+        self._L.sblas_host16_copyto(self._h, _ptr(dense), stride, int(trans))
+        return dense
+
+    def AddMatMat(self, a, m, lda, c, ldc, alpha, beta):
+        if m > 0:
+            _need(a, (m - 1) * lda + self.NumRows(), "a"); _need(c, (m - 1) * ldc + self.NumCols(), "c")
+        _capi.check(self._L.sblas_host16_addmatmat(self._h, _ptr(a), m, lda, _ptr(c), ldc, alpha, beta))
+        return c
+
+    def NumRows(self):
+        return self._L.sblas_host16_num_rows(self._h)
+
+    def NumCols(self):
+        return self._L.sblas_host16_num_cols(self._h)
+
+    def members(self):
+        """(pos uint16, code, table[T+1], T, block_bounds[nb,2], block_index_bounds[nb,2]) -- copies."""
+        n = self._L.sblas_host16_entries(self._h); nb = self._L.sblas_host16_nblocks(self._h)
+        T = self._L.sblas_host16_table_size(self._h)
+        p = [C.c_void_p() for _ in range(5)]
+        self._L.sblas_host16_members(self._h, *[C.byref(x) for x in p])
+
+        def grab(ptr, count, dtype):
+            if not ptr.value or count == 0:
+                return np.zeros(count, dtype)
+            buf = (C.c_char * (count * np.dtype(dtype).itemsize)).from_address(ptr.value)
+            return np.frombuffer(buf, dtype=dtype, count=count).copy()
+
+        return (grab(p[0], n, np.uint16), grab(p[1], n, np.uint8), grab(p[2], T + 1 if T else 0, np.float32), T,
+                grab(p[3], 2 * nb, np.int32).reshape(-1, 2), grab(p[4], 2 * nb, np.int32).reshape(-1, 2))
+
+    def device_matrix(self):
+        h = self._L.sblas_host16_device_matrix(self._h)
+        if not h:
+            raise _capi.SblasError(_capi.ECUDA, self._L.sblas_b200_last_error().decode())
+        return DeviceMatrix(h, owned=False, owner=self)
+

@@ -173,4 +173,58 @@ int sblas_host_load(sblas_host_matrix *h, const char *path) {
     return SBLAS_B200_OK;
 }
 
+
+/* ---- sblas::SparseMatrix<uint16, uint8, float>: two-byte position deltas ---------------------------------------- */
+typedef sblas::SparseMatrix<uint16, uint8, float> HostMatrix16;
+namespace {
+struct MemberView16 {
+    std::vector<uint16_t> pos_index;
+    std::vector<uint8_t> val_index;
+    std::vector<float> val_table;
+    std::vector<std::pair<int32, int32> > block_bounds;
+    std::vector<std::pair<int32, int32> > block_index_bounds;
+    int32 rows, cols;
+};
+static_assert(sizeof(MemberView16) == sizeof(HostMatrix16), "SparseMatrix layout changed");
+inline HostMatrix16 *obj16(sblas_host_matrix16 *h) { return reinterpret_cast<HostMatrix16 *>(h); }
+inline const MemberView16 &view16(const sblas_host_matrix16 *h) { return *reinterpret_cast<const MemberView16 *>(h); }
+}  // namespace
+
+sblas_host_matrix16 *sblas_host16_create(void) { return reinterpret_cast<sblas_host_matrix16 *>(new (std::nothrow) HostMatrix16()); }
+void sblas_host16_free(sblas_host_matrix16 *h) { delete obj16(h); }
+int sblas_host16_copyform(sblas_host_matrix16 *h, const uint8_t *density_matrix, int32_t rows, int32_t cols, int32_t stride,
+                          const float *vals, int32_t val_table_size, int32_t trans) {
+    if (!h || val_table_size < 0 || val_table_size > 255) return SBLAS_B200_EINVAL;
+    obj16(h)->CopyForm(density_matrix, rows, cols, stride, vals, val_table_size, trans ? sblas::SblasTrans : sblas::SblasNoTrans);
+    return SBLAS_B200_OK;
+}
+void sblas_host16_copyto(sblas_host_matrix16 *h, float *density_matrix, int32_t stride, int32_t trans) {
+    obj16(h)->CopyTo(density_matrix, stride, trans ? sblas::SblasTrans : sblas::SblasNoTrans);
+}
+int sblas_host16_addmatmat(sblas_host_matrix16 *h, const float *a, int32_t m, int32_t lda, float *c, int32_t ldc, float alpha,
+                           float beta) {
+    if (!h) return SBLAS_B200_EINVAL;
+    if (obj16(h)->NumCols() == 0 || m <= 0) return SBLAS_B200_OK;
+    sblas_b200_matrix *dev = obj16(h)->DeviceMatrix();
+    if (!dev) return SBLAS_B200_ECUDA;
+    return sblas_b200_addmatmat_host(dev, a, m, lda, c, ldc, alpha, beta);
+}
+int32_t sblas_host16_num_rows(const sblas_host_matrix16 *h) { return reinterpret_cast<const HostMatrix16 *>(h)->NumRows(); }
+int32_t sblas_host16_num_cols(const sblas_host_matrix16 *h) { return reinterpret_cast<const HostMatrix16 *>(h)->NumCols(); }
+int64_t sblas_host16_entries(const sblas_host_matrix16 *h) { return (int64_t)view16(h).pos_index.size(); }
+int32_t sblas_host16_nblocks(const sblas_host_matrix16 *h) { return (int32_t)view16(h).block_bounds.size(); }
+int32_t sblas_host16_table_size(const sblas_host_matrix16 *h) {
+    return view16(h).val_table.empty() ? 0 : (int32_t)view16(h).val_table.size() - 1;
+}
+void sblas_host16_members(const sblas_host_matrix16 *h, const uint16_t **pos_index, const uint8_t **val_index, const float **val_table,
+                          const int32_t **block_bounds, const int32_t **block_index_bounds) {
+    const MemberView16 &v = view16(h);
+    if (pos_index) *pos_index = v.pos_index.data();
+    if (val_index) *val_index = v.val_index.data();
+    if (val_table) *val_table = v.val_table.data();
+    if (block_bounds) *block_bounds = v.block_bounds.empty() ? nullptr : &v.block_bounds[0].first;
+    if (block_index_bounds) *block_index_bounds = v.block_index_bounds.empty() ? nullptr : &v.block_index_bounds[0].first;
+}
+sblas_b200_matrix *sblas_host16_device_matrix(sblas_host_matrix16 *h) { return h ? obj16(h)->DeviceMatrix() : nullptr; }
+
 }  // extern "C"

@@ -95,8 +95,9 @@ SBLAS_TMPL void SBLAS_CLS::CopyForm(const ValIndex_t *density_matrix, int32 rows
     static_assert(block_row_shift == 0, "the B200 build implements the reference's only instantiation: full-height panels");
     Destroy();
     const int32 max_delta = (int32)((1u << (8 * sizeof(PosIndex_t))) - 1u);      // 255 for uint8
-    if (val_table_size < 0 || val_table_size > max_delta) {
-        printf("CopyForm: val_table_size %d outside [0, %d]\n", val_table_size, max_delta);
+    const int32 max_code = (int32)((1u << (8 * sizeof(ValIndex_t) < 31 ? 8 * sizeof(ValIndex_t) : 31)) - 1u);   // the filler's code is val_table_size itself
+    if (val_table_size < 0 || val_table_size > max_delta || val_table_size > max_code) {
+        printf("CopyForm: val_table_size %d outside [0, %d]\n", val_table_size, max_delta < max_code ? max_delta : max_code);
         abort();                                                                   // the reference asserts
     }
     if (val_table_size == 0) return;
@@ -162,11 +163,12 @@ SBLAS_TMPL void SBLAS_CLS::CopyTo(Value_t *density_matrix, int32 stride, SBLAS_T
 }
 
 SBLAS_TMPL sblas_b200_matrix *SBLAS_CLS::DeviceMatrix() {
-    static_assert(std::is_same<PosIndex_t, uint8_t>::value && std::is_same<ValIndex_t, uint8_t>::value &&
-                      std::is_same<Value_t, float>::value,
-                  "device path exists for <uint8, uint8, float>");
+    static_assert((std::is_same<PosIndex_t, uint8_t>::value || std::is_same<PosIndex_t, uint16_t>::value) &&
+                      std::is_same<ValIndex_t, uint8_t>::value && std::is_same<Value_t, float>::value,
+                  "device path exists for <uint8 | uint16, uint8, float>");
     device::StreamView v;
     v.pos_index = pos_index_.data();
+    v.pos_bytes = (int32)sizeof(PosIndex_t);
     v.val_index = val_index_.data();
     v.entries = (int64_t)pos_index_.size();
     v.val_table = val_table_.data();
@@ -245,5 +247,8 @@ SBLAS_TMPL bool SBLAS_CLS::SelfTest() {
 }
 
 template class SparseMatrix<uint8, uint8, float>;
+// Two-byte position deltas: the reference has the code path (sparse-matrix.cc:24) but never
+// instantiates it (:315).  No fillers below gaps of 65 535: the hypersparse end of the density sweep.
+template class SparseMatrix<uint16, uint8, float>;
 
 }  // namespace sblas

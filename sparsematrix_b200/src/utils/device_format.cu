@@ -96,8 +96,9 @@ __device__ __forceinline__ uint32_t warp_inclusive_scan(uint32_t v, int lane) {
 }
 
 // K-up1
+template <typename PosT>
 __global__ void __launch_bounds__(32 * kWarpsPerCta)
-seg_delta_sum_kernel(const uint8_t *__restrict__ pos, const int32_t *__restrict__ seg_begin,
+seg_delta_sum_kernel(const PosT *__restrict__ pos, const int32_t *__restrict__ seg_begin,
                      const int32_t *__restrict__ seg_end, int nseg, uint32_t *__restrict__ seg_pos0) {
     const int seg = blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (seg >= nseg) return;
@@ -122,8 +123,9 @@ __global__ void panel_seg_scan_kernel(const int32_t *__restrict__ panel_seg_firs
 }
 
 // K-up3
+template <typename PosT>
 __global__ void __launch_bounds__(32 * kWarpsPerCta)
-seg_count_kernel(const uint8_t *__restrict__ pos, const uint8_t *__restrict__ code, int T,
+seg_count_kernel(const PosT *__restrict__ pos, const uint8_t *__restrict__ code, int T,
                  const int32_t *__restrict__ seg_begin, const int32_t *__restrict__ seg_end,
                  const int32_t *__restrict__ seg_panel, const int32_t *__restrict__ panel_col_off,
                  const uint32_t *__restrict__ seg_pos0, int nseg, int n, int k, int32_t *__restrict__ seg_hist,
@@ -205,8 +207,9 @@ row_ptr_scan_kernel(const int32_t *__restrict__ row_len, int n, int32_t *__restr
 }
 
 // K-up6
+template <typename PosT>
 __global__ void __launch_bounds__(32 * kWarpsPerCta)
-seg_scatter_kernel(const uint8_t *__restrict__ pos, const uint8_t *__restrict__ code, int T,
+seg_scatter_kernel(const PosT *__restrict__ pos, const uint8_t *__restrict__ code, int T,
                    const int32_t *__restrict__ seg_begin, const int32_t *__restrict__ seg_end,
                    const int32_t *__restrict__ seg_panel, const uint32_t *__restrict__ seg_pos0, int nseg,
                    const int32_t *__restrict__ panel_col_off, const int32_t *__restrict__ seg_hist,
@@ -458,7 +461,7 @@ static void release(sblas_b200_matrix *mat) {
 
 // Scratch device arrays of one upload, freed on every exit path.
 struct UploadScratch {
-    uint8_t *pos = nullptr, *code = nullptr;
+    uint8_t *pos = nullptr, *code = nullptr;           // pos: pos_bytes per entry
     int32_t *seg_begin = nullptr, *seg_end = nullptr, *seg_panel = nullptr, *panel_seg_first = nullptr,
             *panel_col_off = nullptr, *seg_hist = nullptr, *row_len = nullptr;
     uint32_t *seg_pos0 = nullptr;
@@ -470,7 +473,8 @@ struct UploadScratch {
     }
 };
 
-static int upload_stream_impl(const uint8_t *pos_index, const uint8_t *val_index, int64_t entries,
+// pos_bytes = sizeof(PosIndex_t): 1 for the reference's instantiation, 2 for SparseMatrix<uint16, uint8, float>
+static int upload_stream_impl(const void *pos_index, int pos_bytes, const uint8_t *val_index, int64_t entries,
                               const float *val_table, int32_t T, const int32_t *block_bounds,
                               const int32_t *block_index_bounds, int32_t nblocks, int32_t rows, int32_t cols,
                               int32_t col_begin, int32_t col_end, sblas_b200_matrix *mat) {
@@ -514,9 +518,10 @@ static int upload_stream_impl(const uint8_t *pos_index, const uint8_t *val_index
     SB_CUDA(cudaMalloc((void **)&sc.fillers, 16));
     SB_CUDA(cudaMemset(sc.fillers, 0, 16));
     if (nseg) {
-        SB_CUDA(cudaMalloc((void **)&sc.pos, (size_t)mat->entries));
+        SB_CUDA(cudaMalloc((void **)&sc.pos, (size_t)mat->entries * pos_bytes));
         SB_CUDA(cudaMalloc((void **)&sc.code, (size_t)mat->entries));
-        SB_CUDA(cudaMemcpy(sc.pos, pos_index + e_begin, (size_t)mat->entries, cudaMemcpyDefault));   // host streams, or the device-resident ones of copyform.cu
+        SB_CUDA(cudaMemcpy(sc.pos, static_cast<const uint8_t *>(pos_index) + e_begin * pos_bytes, (size_t)mat->entries * pos_bytes,
+                           cudaMemcpyDefault));                  // host streams, or the device-resident ones of copyform.cu
         SB_CUDA(cudaMemcpy(sc.code, val_index + e_begin, (size_t)mat->entries, cudaMemcpyDefault));
         SB_CUDA(cudaMalloc((void **)&sc.seg_begin, (size_t)nseg * 4));
         SB_CUDA(cudaMalloc((void **)&sc.seg_end, (size_t)nseg * 4));
@@ -532,10 +537,14 @@ static int upload_stream_impl(const uint8_t *pos_index, const uint8_t *val_index
         SB_CUDA(cudaMemcpy(sc.panel_col_off, panel_col_off.data(), (size_t)np * 4, cudaMemcpyHostToDevice));
 
         const int seg_grid = (nseg + kWarpsPerCta - 1) / kWarpsPerCta;
-        SB_LAUNCH(seg_delta_sum_kernel, seg_grid, 32 * kWarpsPerCta, 0, 0, sc.pos, sc.seg_begin, sc.seg_end, nseg, sc.seg_pos0);
+        const uint16_t *pos16 = reinterpret_cast<const uint16_t *>(sc.pos);
+        if (pos_bytes == 2) SB_LAUNCH(seg_delta_sum_kernel<uint16_t>, seg_grid, 32 * kWarpsPerCta, 0, 0, pos16, sc.seg_begin, sc.seg_end, nseg, sc.seg_pos0);
+        else SB_LAUNCH(seg_delta_sum_kernel<uint8_t>, seg_grid, 32 * kWarpsPerCta, 0, 0, sc.pos, sc.seg_begin, sc.seg_end, nseg, sc.seg_pos0);
         SB_LAUNCH(panel_seg_scan_kernel, (np + 127) / 128, 128, 0, 0, sc.panel_seg_first, np, sc.seg_pos0);
-        SB_LAUNCH(seg_count_kernel, seg_grid, 32 * kWarpsPerCta, 0, 0, sc.pos, sc.code, T, sc.seg_begin, sc.seg_end,
-                  sc.seg_panel, sc.panel_col_off, sc.seg_pos0, nseg, n, mat->k, sc.seg_hist, sc.fillers);
+        if (pos_bytes == 2) SB_LAUNCH(seg_count_kernel<uint16_t>, seg_grid, 32 * kWarpsPerCta, 0, 0, pos16, sc.code, T, sc.seg_begin, sc.seg_end,
+                                      sc.seg_panel, sc.panel_col_off, sc.seg_pos0, nseg, n, mat->k, sc.seg_hist, sc.fillers);
+        else SB_LAUNCH(seg_count_kernel<uint8_t>, seg_grid, 32 * kWarpsPerCta, 0, 0, sc.pos, sc.code, T, sc.seg_begin, sc.seg_end,
+                       sc.seg_panel, sc.panel_col_off, sc.seg_pos0, nseg, n, mat->k, sc.seg_hist, sc.fillers);
         SB_LAUNCH(panel_bin_scan_kernel, np, kPanelWidth, 0, 0, sc.panel_seg_first, sc.panel_col_off, sc.seg_hist,
                   sc.row_len, n);
         SB_CHECK_LAUNCH();
@@ -568,16 +577,21 @@ static int upload_stream_impl(const uint8_t *pos_index, const uint8_t *val_index
     if (e != cudaSuccess) return cuda_fail(e, "row_ptr copy", __FILE__, __LINE__);
     if (nseg) {
         const int seg_grid = (nseg + kWarpsPerCta - 1) / kWarpsPerCta;
-        SB_LAUNCH(seg_scatter_kernel, seg_grid, 32 * kWarpsPerCta, 0, 0, sc.pos, sc.code, T, sc.seg_begin, sc.seg_end,
-                  sc.seg_panel, sc.seg_pos0, nseg, sc.panel_col_off, sc.seg_hist, mat->d_row_ptr, n, mat->k,
-                  mat->d_col, mat->d_code);
+        if (pos_bytes == 2)
+            SB_LAUNCH(seg_scatter_kernel<uint16_t>, seg_grid, 32 * kWarpsPerCta, 0, 0, reinterpret_cast<const uint16_t *>(sc.pos), sc.code, T,
+                      sc.seg_begin, sc.seg_end, sc.seg_panel, sc.seg_pos0, nseg, sc.panel_col_off, sc.seg_hist, mat->d_row_ptr, n, mat->k,
+                      mat->d_col, mat->d_code);
+        else
+            SB_LAUNCH(seg_scatter_kernel<uint8_t>, seg_grid, 32 * kWarpsPerCta, 0, 0, sc.pos, sc.code, T, sc.seg_begin, sc.seg_end,
+                      sc.seg_panel, sc.seg_pos0, nseg, sc.panel_col_off, sc.seg_hist, mat->d_row_ptr, n, mat->k,
+                      mat->d_col, mat->d_code);
         SB_CHECK_LAUNCH();
     }
     SB_CUDA(cudaDeviceSynchronize());
     return plan_spmv(mat, h_row_ptr.data());
 }
 
-static int check_stream_args(const uint8_t *pos_index, const uint8_t *val_index, int64_t entries, const float *val_table,
+static int check_stream_args(const void *pos_index, const uint8_t *val_index, int64_t entries, const float *val_table,
                              int32_t T, const int32_t *block_bounds, const int32_t *block_index_bounds, int32_t nblocks,
                              int32_t rows, int32_t cols, sblas_b200_matrix **out) {
     if (!out) return fail(SBLAS_B200_EINVAL, "out is null");
@@ -611,7 +625,7 @@ int sblas_b200_device_count(int32_t *count) {
     return SBLAS_B200_OK;
 }
 
-int sblas_b200_upload_slab(const uint8_t *pos_index, const uint8_t *val_index, int64_t entries, const float *val_table,
+static int upload_slab_any(const void *pos_index, int pos_bytes, const uint8_t *val_index, int64_t entries, const float *val_table,
                            int32_t T, const int32_t *block_bounds, const int32_t *block_index_bounds, int32_t nblocks,
                            int32_t rows, int32_t cols, int32_t col_begin, int32_t col_end, int32_t device,
                            sblas_b200_matrix **out) {
@@ -625,11 +639,27 @@ int sblas_b200_upload_slab(const uint8_t *pos_index, const uint8_t *val_index, i
     sblas_b200_matrix *mat = new (std::nothrow) sblas_b200_matrix();
     if (!mat) return fail(SBLAS_B200_ENOMEM, "host allocation failed");
     mat->device = device;
-    rc = upload_stream_impl(pos_index, val_index, entries, val_table, T, block_bounds, block_index_bounds, nblocks, rows,
+    rc = upload_stream_impl(pos_index, pos_bytes, val_index, entries, val_table, T, block_bounds, block_index_bounds, nblocks, rows,
                             cols, col_begin, col_end, mat);
     if (rc != SBLAS_B200_OK) { release(mat); return rc; }
     *out = mat;
     return SBLAS_B200_OK;
+}
+
+int sblas_b200_upload_slab(const uint8_t *pos_index, const uint8_t *val_index, int64_t entries, const float *val_table,
+                           int32_t T, const int32_t *block_bounds, const int32_t *block_index_bounds, int32_t nblocks,
+                           int32_t rows, int32_t cols, int32_t col_begin, int32_t col_end, int32_t device,
+                           sblas_b200_matrix **out) {
+    return upload_slab_any(pos_index, 1, val_index, entries, val_table, T, block_bounds, block_index_bounds, nblocks, rows, cols,
+                           col_begin, col_end, device, out);
+}
+
+int sblas_b200_upload_slab16(const uint16_t *pos_index, const uint8_t *val_index, int64_t entries, const float *val_table,
+                             int32_t T, const int32_t *block_bounds, const int32_t *block_index_bounds, int32_t nblocks,
+                             int32_t rows, int32_t cols, int32_t col_begin, int32_t col_end, int32_t device,
+                             sblas_b200_matrix **out) {
+    return upload_slab_any(pos_index, 2, val_index, entries, val_table, T, block_bounds, block_index_bounds, nblocks, rows, cols,
+                           col_begin, col_end, device, out);
 }
 
 int sblas_b200_upload(const uint8_t *pos_index, const uint8_t *val_index, int64_t entries, const float *val_table,

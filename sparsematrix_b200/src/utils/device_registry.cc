@@ -35,8 +35,11 @@ sblas_b200_matrix *Acquire(const void *owner, const StreamView &v) {
     auto it = table().find(key);
     if (it != table().end()) return it->second;
     sblas_b200_matrix *mat = nullptr;
-    const int rc = sblas_b200_upload(v.pos_index, v.val_index, v.entries, v.val_table, v.valid_table_size, v.block_bounds,
-                                     v.block_index_bounds, v.nblocks, v.rows, v.cols, dev, &mat);
+    const int rc = v.pos_bytes == 2
+        ? sblas_b200_upload_slab16(static_cast<const uint16_t *>(v.pos_index), v.val_index, v.entries, v.val_table, v.valid_table_size,
+                                   v.block_bounds, v.block_index_bounds, v.nblocks, v.rows, v.cols, 0, v.cols, dev, &mat)
+        : sblas_b200_upload(static_cast<const uint8_t *>(v.pos_index), v.val_index, v.entries, v.val_table, v.valid_table_size,
+                            v.block_bounds, v.block_index_bounds, v.nblocks, v.rows, v.cols, dev, &mat);
     if (rc != SBLAS_B200_OK) {
         printf("sblas_b200: device upload failed (%d): %s\n", rc, sblas_b200_last_error());
         return nullptr;

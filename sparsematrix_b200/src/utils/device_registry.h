@@ -15,7 +15,8 @@ namespace sblas {
 namespace device {
 
 struct StreamView {                 // the compressed members, as plain pointers
-    const uint8_t *pos_index;
+    const void *pos_index;          // pos_bytes per entry
+    int32_t pos_bytes;              // sizeof(PosIndex_t): 1 or 2
     const uint8_t *val_index;
     int64_t entries;
     const float *val_table;

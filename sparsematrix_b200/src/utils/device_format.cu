@@ -339,7 +339,10 @@ int plan_spmv(sblas_b200_matrix *mat, const int32_t *h_row_ptr) {
     mat->spmv_lanes = lanes;
     // a sub-warp streams rows up to 512 entries per lane; at 256 per lane the 16384^2 / 50 % case had half
     // of its rows (about 8192 entries) on the split-row path and ran 207 instead of 158 us
-    mat->long_threshold = std::max(1024, 512 * lanes);
+    // -- with few lanes per row (short mean, i.e. skewed lengths) a row of 1024 entries is a chain of 128 dependent
+    // iterations of one lane pair, ~130 us whatever else the kernel does: a 1/8 slab of the power-law matrix ran 194 us
+    // with the threshold at 1024 and 108 us at 256 (r02); such rows go to the split-row path earlier
+    mat->long_threshold = lanes >= 8 ? 512 * lanes : std::max(256, 128 * lanes);
     if (const char *env = getenv("SBLAS_B200_LONG_THRESHOLD")) {
         const int v = atoi(env);
         if (v > 0) mat->long_threshold = v;

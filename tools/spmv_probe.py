@@ -13,7 +13,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import sparsematrix_b200 as sb  # noqa: E402
 from sparsematrix_b200 import gen  # noqa: E402
 
-n = k = int(os.environ.get("PROBE_N", 1 << 23))
+n = int(os.environ.get("PROBE_N", 1 << 23))
+k = int(os.environ.get("PROBE_K", n))
 row_ptr, col, code = gen.powerlaw_csr(n, k, 14)
 tab = gen.codebook()
 x = torch.from_numpy(gen.dense_uniform((1, k), 2)).cuda()

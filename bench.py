@@ -561,6 +561,7 @@ def measure(name, args, cx):
                          "peak_source": "tensor: nominal dense TF32 = half of the 2250 TFLOP/s bf16 figure (B200_PROFILING.md); "
                                         "MEASURED_PEAKS.json has cuBLAS bf16 only: %s TFLOP/s burst, i.e. %.0f for TF32; hbm: %s"
                                         % (cx.bf16_measured, (cx.bf16_measured or 0) / 2, peak_src),
+                         "frac_of_half_measured_bf16": (tc_ach / (cx.bf16_measured / 2)) if cx.bf16_measured else None,
                          "useful_tflops": flops_k / (kern_us * 1e-6) / 1e12})
         clk = clocks.summary()
         sm_hz = (clk.get("sm_mhz") or 1965.0) * 1e6

@@ -1,5 +1,5 @@
 // async_copy.cuh -- mbarrier and bulk-copy (TMA engine) helpers shared by the kernels that stage
-// their operands through shared memory (spmm_tile.cu, spmv_wide.cu).
+// their operands through shared memory (spmm_tile.cu, spmm_tc.cu).
 #ifndef SBLAS_B200_ASYNC_COPY_CUH_
 #define SBLAS_B200_ASYNC_COPY_CUH_
 

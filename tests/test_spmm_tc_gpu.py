@@ -157,3 +157,36 @@ def test_tensor_core_spmm_products_of_different_shapes_share_one_workspace():
     for m in (256, 512, 256, 64, 512):
         _check(dev, s, m, 1.0, 1.0, seed=m)
     dev.free()
+
+
+def test_tensor_core_spmm_can_be_captured_into_a_cuda_graph():
+    """Like the other kernels (tests/test_gpu_parity.py, graphs): after one eager call per shape the product records into a
+    CUDA graph and replays with the same bits; the call id of the non-finite-x flag is baked into the recording, which is fine."""
+    import torch
+    n, k, m = 512, 1024, 128
+    codes = gen.codes_bernoulli(n, k, 0.3, seed=97)
+    s = O.copyform(codes, n, k, k, gen.codebook(255, 1), 255, True)
+    dev = sb.DeviceMatrix.upload(s.pos, s.code, s.table, s.T, s.block_bounds, s.block_index_bounds, s.rows, s.cols)
+    a = torch.from_numpy(gen.dense_uniform((m, k), 1)).cuda()
+    c0 = torch.from_numpy(gen.dense_uniform((m, n), 2)).cuda()
+    os.environ["SBLAS_B200_SPMM_TC"] = "1"
+    try:
+        want = c0.clone()
+        dev.addmatmat_dev(a, m, k, want, n, 1.3, 0.7)
+        torch.cuda.synchronize()
+        assert dev.last_product()["kernel"].startswith("spmm_tc")
+        c = c0.clone()
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=side):
+            dev.addmatmat_dev(a, m, k, c, n, 1.3, 0.7, stream=side.cuda_stream)
+        assert dev.last_product()["kernel"].startswith("spmm_tc")
+        for rep in range(3):
+            c.copy_(c0)
+            graph.replay()
+            torch.cuda.synchronize()
+            assert_bits_equal(c.cpu().numpy(), want.cpu().numpy(), f"graph replay {rep}")
+    finally:
+        os.environ.pop("SBLAS_B200_SPMM_TC", None)
+    dev.free()

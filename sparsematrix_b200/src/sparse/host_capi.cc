@@ -161,6 +161,22 @@ int sblas_host_load(sblas_host_matrix *h, const char *path) {
     if ((int64_t)expect != hd.entries) return SBLAS_B200_EFORMAT;
     for (size_t i = 0; i < in.val_index.size(); ++i)
         if ((int32_t)in.val_index[i] > hd.table_size) return SBLAS_B200_EFORMAT;
+    // every stored entry must decode to a position inside the matrix (CopyTo has no bounds check, like the reference:
+    // a crafted file with a matching checksum would otherwise write outside the caller's dense buffer), and a real
+    // entry after the first of a panel has a delta >= 1 (two entries on one position would collapse in the dense-code SpMV)
+    for (int32_t b = 0; b < hd.nblocks; ++b) {
+        const int32_t col_off = in.block_bounds[b].second;
+        const int32_t width = hd.cols - col_off < 256 ? hd.cols - col_off : 256;
+        int64_t lin = 0;
+        bool first = true;
+        for (int32_t e = in.block_index_bounds[b].first; e < in.block_index_bounds[b].second; ++e) {
+            lin += in.pos_index[e];
+            if ((int32_t)in.val_index[e] == hd.table_size) continue;          // filler
+            if ((lin >> 8) >= hd.rows || (int32_t)(lin & 255) >= width) return SBLAS_B200_EFORMAT;
+            if (!first && in.pos_index[e] == 0) return SBLAS_B200_EFORMAT;
+            first = false;
+        }
+    }
     obj(h)->Destroy();                                    // drops the device copy, like CopyForm (sparse-matrix.cc:22)
     MemberView &out = mutable_view(h);
     out.pos_index.swap(in.pos_index);

@@ -191,6 +191,29 @@ def test_save_and_load_round_trip_and_reject_corruption(tmp_path):
         with pytest.raises(sb.SblasError) as ei:
             keep.Load(str(tmp_path / "missing.sblas"))
         assert ei.value.code == _capi.EIO
+    # a crafted file whose checksum matches but whose positions run past the matrix, or repeat a position: rejected before
+    # anything can decode it (the host CopyTo has no bounds check, like the reference's)
+    def fnv1a(data):
+        h = 14695981039346656037
+        for byte in data:
+            h = ((h ^ byte) * 1099511628211) & 0xFFFFFFFFFFFFFFFF
+        return h
+    S = sb.SparseMatrix(codes, n, k, k, tab, 255, sb.SparseMatrix.NoTrans)
+    path = str(tmp_path / "good.sblas")
+    S.Save(path)
+    raw = bytearray(open(path, "rb").read())
+    pos, code, table, T, bb, bib = S.members()
+    pos_off = 32 + 4 * (T + 1) + 16 * bb.shape[0]
+    assert bytes(raw[pos_off: pos_off + 16]) == pos[:16].tobytes()
+    for name, edit in (("past the last row", lambda b: b.__setitem__(slice(pos_off + int(bib[-1, 0]), pos_off + int(bib[-1, 1])), b"\xff" * int(bib[-1, 1] - bib[-1, 0]))),
+                       ("repeated position", lambda b: b.__setitem__(pos_off + 1, 0))):
+        body = bytearray(raw[:-8])
+        edit(body)
+        crafted = str(tmp_path / "crafted.sblas")
+        open(crafted, "wb").write(bytes(body) + fnv1a(body).to_bytes(8, "little"))
+        with pytest.raises(sb.SblasError) as ei:
+            keep.Load(crafted)
+        assert ei.value.code == _capi.EFORMAT, name
     E = sb.SparseMatrix()                                      # empty object
     E.Save(str(tmp_path / "empty.sblas"))
     F = sb.SparseMatrix(codes, n, k, k, tab, 255, 0)

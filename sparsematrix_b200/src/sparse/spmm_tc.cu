@@ -147,31 +147,55 @@ __device__ __forceinline__ void tmem_ld_sum(uint32_t taddr, float (&v)[32]) {
     }
 }
 
+#ifdef EXP_TC_TIMELINE
+// experiment build only (tools/build_variant.sh): phase stamps of every CTA of the last contraction, dumped at exit
+__device__ unsigned long long g_tc_timeline[4096 * 8];
+__device__ __forceinline__ unsigned long long tc_gtime() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define TCL(p, tid) do { if (threadIdx.x == (tid)) { const unsigned b_ = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x; \
+                         if (b_ < 4096) g_tc_timeline[b_ * 8 + (p)] = tc_gtime(); } } while (0)
+#else
+#define TCL(p, tid) do { } while (0)
+#endif
+
 // ---- X -> operand images ----------------------------------------------------------------------------------------
 // xh / xl [m tile][k block][N rows x 128 bytes]: row i of a tile = dense row m0 + i (a row of A: contiguous in k),
 // its eight 16-byte chunks stored at chunk ^ (i & 7) -- the SWIZZLE_128B image the MMA reads, so the main kernel moves
 // a tile with one plain bulk copy.  Rows beyond m and columns beyond k are zeros.  Non-finite values raise the flag.
 __global__ void __launch_bounds__(256)
 tc_split_x_kernel(const float *__restrict__ a, int m, int k, int lda, int n_tile, int nkb, float *__restrict__ xh,
-                  float *__restrict__ xl, uint32_t *__restrict__ flag, uint32_t call_id) {
+                  float *__restrict__ xl, uint32_t *__restrict__ flag, uint32_t call_id, int vec) {
     const int kb = blockIdx.x, mt = blockIdx.y;
     const size_t tile = ((size_t)mt * nkb + kb) * n_tile * kTcBK;
-    bool bad = false;
-    for (int t = threadIdx.x; t < n_tile * 8; t += 256) {
-        const int i = t >> 3, ch = t & 7;
-        const int gi = mt * n_tile + i, r0 = kb * kTcBK + ch * 4;
-        float v[4];
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // the contraction may set up its CTAs meanwhile
+    // one (row, 16-byte chunk) per thread: grid.z x 256 threads cover the n_tile x 8 chunks of the tile
+    const int t = blockIdx.z * 256 + threadIdx.x;
+    if (t >= n_tile * 8) return;
+    const int i = t >> 3, ch = t & 7;
+    const int gi = mt * n_tile + i, r0 = kb * kTcBK + ch * 4;
+    float v[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+    if (gi < m) {
+        const float *src = a + (size_t)gi * lda + r0;
+        if (vec && r0 + 3 < k) {
+            const float4 q = __ldg(reinterpret_cast<const float4 *>(src));
+            v[0] = q.x; v[1] = q.y; v[2] = q.z; v[3] = q.w;
+        } else {
 #pragma unroll
-        for (int u = 0; u < 4; ++u) v[u] = (gi < m && r0 + u < k) ? a[(size_t)gi * lda + r0 + u] : 0.0f;
-        float4 hi, lo;
-        hi.x = tf32_floor(v[0]); hi.y = tf32_floor(v[1]); hi.z = tf32_floor(v[2]); hi.w = tf32_floor(v[3]);
-        lo.x = tf32_floor(v[0] - hi.x); lo.y = tf32_floor(v[1] - hi.y); lo.z = tf32_floor(v[2] - hi.z); lo.w = tf32_floor(v[3] - hi.w);
-        bad |= !(isfinite(v[0]) && isfinite(v[1]) && isfinite(v[2]) && isfinite(v[3]));
-        const size_t off = tile + (size_t)i * kTcBK + ((ch ^ (i & 7)) << 2);
-        *reinterpret_cast<float4 *>(xh + off) = hi;
-        *reinterpret_cast<float4 *>(xl + off) = lo;
+            for (int u = 0; u < 4; ++u)
+                if (r0 + u < k) v[u] = src[u];
+        }
     }
-    if (bad) atomicExch(flag, call_id);
+    float4 hi, lo;
+    hi.x = tf32_floor(v[0]); hi.y = tf32_floor(v[1]); hi.z = tf32_floor(v[2]); hi.w = tf32_floor(v[3]);
+    lo.x = tf32_floor(v[0] - hi.x); lo.y = tf32_floor(v[1] - hi.y); lo.z = tf32_floor(v[2] - hi.z); lo.w = tf32_floor(v[3] - hi.w);
+    const bool bad = !(isfinite(v[0]) && isfinite(v[1]) && isfinite(v[2]) && isfinite(v[3]));
+    const size_t off = tile + (size_t)i * kTcBK + ((ch ^ (i & 7)) << 2);
+    *reinterpret_cast<float4 *>(xh + off) = hi;
+    *reinterpret_cast<float4 *>(xl + off) = lo;
+    if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicExch(flag, call_id);
 }
 
 // ---- the contraction ----------------------------------------------------------------------------------------------
@@ -194,7 +218,7 @@ spmm_tc_kernel(const uint8_t *__restrict__ dense, int64_t kpad, const int32_t *_
     // (round-robin over 256 / N_TILE accumulators was measured and bought nothing once the MMAs were issued back to back)
     constexpr int NACC = 1;
     extern __shared__ uint8_t smem_raw[];
-    if (*flag == call_id) return;                               // non-finite x: tc_fallback_kernel computes this product
+    TCL(0, 0);
     const uint32_t raw = smem_u32(smem_raw);
     uint8_t *sm = smem_raw + (((raw + 1023u) & ~1023u) - raw);
     const uint32_t sm_addr = smem_u32(sm);
@@ -211,9 +235,22 @@ spmm_tc_kernel(const uint8_t *__restrict__ dense, int64_t kpad, const int32_t *_
     const int kb_lo = 4 * (int)((int64_t)(nkb / 4) * split / ksplit), kb_hi = 4 * (int)((int64_t)(nkb / 4) * (split + 1) / ksplit);
     const int steps = kb_hi - kb_lo;
 
-    for (int i = threadIdx.x; i < 256 * kTcTabCopies; i += kTcThreads) {
-        const int cd = i / kTcTabCopies;
-        tab_s[i] = cd < T ? table[cd] * alpha : 0.0f;           // val_table[code] * alpha (kernel.cc:791); split when expanded
+    // one global load per thread, in flight during the set-up below (a loop over the 4096 copies was 3.6 us of dependent
+    // loads at the head of every CTA, profiles/r02_spmm_tc.md)
+    const float tab_mine = (threadIdx.x < 256 && (int)threadIdx.x < T) ? __ldg(table + threadIdx.x) * alpha : 0.0f;   // val_table[code] * alpha (kernel.cc:791); split when expanded
+    // the expanders' first line of codes travels meanwhile as well
+    const int e_set = warp >> 2, e_r = (warp & 3) * 32 + lane, e_j = j0 + e_r;
+    const bool e_have = warp < kTcEWarps && e_j < n && steps > 0 && !(dbg & 1);
+    const uint8_t *e_src = dense + (size_t)min(e_j, n - 1) * kpad + (size_t)kb_lo * kTcBK;
+    uint4 nxt[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+        nxt[u] = e_have ? __ldg(reinterpret_cast<const uint4 *>(e_src) + 2 * e_set + (u & 1) + 4 * (u >> 1))
+                        : make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+    if (threadIdx.x < 256) {
+        const float4 q = make_float4(tab_mine, tab_mine, tab_mine, tab_mine);
+#pragma unroll
+        for (int cpy = 0; cpy < kTcTabCopies / 4; ++cpy) reinterpret_cast<float4 *>(tab_s + threadIdx.x * kTcTabCopies)[cpy] = q;
     }
     if (threadIdx.x == 0) {
         for (int s = 0; s < XS; ++s) { mbar_init(&full_x[s], 1); mbar_init(&empty_x[s], 1); }
@@ -221,6 +258,11 @@ spmm_tc_kernel(const uint8_t *__restrict__ dense, int64_t kpad, const int32_t *_
         mbar_init(acc_full, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    // Launched programmatically dependent on tc_split_x_kernel: the set-up and the expansion of the first W operands run
+    // while that kernel drains.  What it wrote is read behind a griddepcontrol.wait: the X images by the producer warp,
+    // the flag by the epilogue (non-finite x: nothing is stored, tc_fallback_kernel computes the product).
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // the fallback kernel may be set up as well
+    TCL(1, 0);
     if (warp == kTcEWarps) {                                    // all of tensor memory: one CTA per SM
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tmem_slot)));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
@@ -230,10 +272,12 @@ spmm_tc_kernel(const uint8_t *__restrict__ dense, int64_t kpad, const int32_t *_
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem = *tmem_slot;
     const uint32_t tmem_w = tmem + 256u;                        // the A-operand ring
+    TCL(2, 0);
 
     if (warp == kTcEWarps) {
         // ---- X producer (the whole warp walks the loop, one elected lane issues) ----
         const float *xh_t = xh + ((size_t)mt * nkb + kb_lo) * N_TILE * kTcBK, *xl_t = xl + ((size_t)mt * nkb + kb_lo) * N_TILE * kTcBK;
+        asm volatile("griddepcontrol.wait;" ::: "memory");     // the X images are complete
         for (int it = 0; it < steps; ++it) {
             const int s = it % XS;
             if (it >= XS) mbar_wait_or_trap(&empty_x[s], (uint32_t)((it / XS - 1) & 1));
@@ -257,6 +301,7 @@ spmm_tc_kernel(const uint8_t *__restrict__ dense, int64_t kpad, const int32_t *_
             mbar_wait_or_trap(&full_w[sw], pw);
             mbar_wait_or_trap(&full_x[sx], px);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            if (it == 0) TCL(3, (kTcEWarps + 1) * 32);
             if (elect_one()) {
                 const uint64_t b_hi = desc0 + (uint64_t)((sx * STAGE_BYTES) >> 4), b_lo = b_hi + (X_BYTES >> 4);
                 const uint32_t w_hi = tmem_w + (uint32_t)sw * 64u, w_lo = w_hi + 32u;
@@ -286,19 +331,14 @@ spmm_tc_kernel(const uint8_t *__restrict__ dense, int64_t kpad, const int32_t *_
     } else {
         // ---- W expanders (one thread per W row of the block = its tensor-memory lane; two sets of four warps take
         //      alternate steps), then the epilogue ----
-        const int set = warp >> 2, quad = warp & 3;
-        const int r = quad * 32 + lane, j = j0 + r;
-        const uint8_t *src = dense + (size_t)min(j, n - 1) * kpad + (size_t)kb_lo * kTcBK;
+        const int set = e_set, quad = warp & 3;
+        const int r = e_r, j = e_j;
+        const uint8_t *src = e_src;
         const bool have = j < n;
-        const uint4 none = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
         const float *tab_l = tab_s + (lane & (kTcTabCopies - 1));
         const uint32_t t_row = tmem_w + ((uint32_t)(quad * 32) << 16);
         // the codes of four steps are one 128-byte line of the row; this set uses steps set and set + 2 of it (32 bytes each).
-        // The next line travels while this one is expanded.
-        uint4 nxt[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u)
-            nxt[u] = (have && steps > 0 && !(dbg & 1)) ? __ldg(reinterpret_cast<const uint4 *>(src) + 2 * set + (u & 1) + 4 * (u >> 1)) : none;
+        // The next line travels while this one is expanded (the first was requested at the head of the kernel).
         for (int it0 = 0; it0 < steps; it0 += 4) {
             uint4 cur[4];
 #pragma unroll
@@ -341,9 +381,14 @@ spmm_tc_kernel(const uint8_t *__restrict__ dense, int64_t kpad, const int32_t *_
         const int len = have ? row_ptr[j + 1] - row_ptr[j] : 0;
         if (steps > 0) mbar_wait_or_trap(acc_full, 0u);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        TCL(4, 0);
+        asm volatile("griddepcontrol.wait;" ::: "memory");     // (long since complete) the flag below is the split kernel's
+        const bool flagged = __ldcg(flag) == call_id;
         const uint32_t t_lane = tmem + ((uint32_t)(quad * 32) << 16);
         const bool touch = have && !(len == 0 && beta == 1.0f);        // S column without entries, no scale: untouched
-        if (ksplit == 1) {
+        if (flagged) {
+            // non-finite x: the accumulators hold NaNs, nothing leaves this kernel
+        } else if (ksplit == 1) {
             for (int col0 = 32 * set; col0 < N_TILE && m0 + col0 < m; col0 += 64) {
                 float acc[32], c_old[32];
                 tmem_ld_sum<NACC, N_TILE>(t_lane + col0, acc);
@@ -378,14 +423,22 @@ spmm_tc_kernel(const uint8_t *__restrict__ dense, int64_t kpad, const int32_t *_
 #pragma unroll
                 for (int t = 0; t < 32; ++t) mine[(size_t)(col0 + t) * kTcM + r] = acc[t];
             }
-            __threadfence();
-            asm volatile("bar.sync 1, 256;" ::: "memory");      // the eight epilogue warps
-            if (threadIdx.x == 0) *last_slot = atomicAdd(&counters[tile_id], 1u) == (uint32_t)(ksplit - 1) ? 1u : 0u;
-            asm volatile("bar.sync 1, 256;" ::: "memory");
-            if (*last_slot) {
+            // counters == nullptr: the whole grid is one wave of CTAs and tc_fixup_kernel adds the shares with every SM (here
+            // the last CTA of each tile would do it alone, all of them at the same time at the end of the only wave)
+            if (counters != nullptr) {
+                __threadfence();
+                asm volatile("bar.sync 1, 256;" ::: "memory");  // the eight epilogue warps
+                if (threadIdx.x == 0) *last_slot = atomicAdd(&counters[tile_id], 1u) == (uint32_t)(ksplit - 1) ? 1u : 0u;
+                asm volatile("bar.sync 1, 256;" ::: "memory");
+            }
+            TCL(5, 0);
+            if (counters != nullptr && *last_slot) {
                 __threadfence();
                 const float *all = partial + tile_id * ksplit * (size_t)N_TILE * kTcM;
-                constexpr int CU = 8;                           // columns per step: their loads travel together
+                // 16 columns per step and three more shares at a time: up to 80 loads of a thread travel together (the loop
+                // is a chain of L2 round trips otherwise: cfg2 spent half of its 43 us here with 8 columns and one share
+                // at a time, profiles/r02_spmm_tc.md).  The order of the additions stays share 0, 1, 2, ...
+                constexpr int CU = 16, SG = 3;
                 for (int col0 = CU * set; col0 < N_TILE && m0 + col0 < m; col0 += 2 * CU) {
                     float sum[CU], v[CU];
 #pragma unroll
@@ -393,12 +446,20 @@ spmm_tc_kernel(const uint8_t *__restrict__ dense, int64_t kpad, const int32_t *_
                         sum[u] = __ldcg(all + (size_t)(col0 + u) * kTcM + r);
                         v[u] = (touch && !red && m0 + col0 + u < m) ? c[(size_t)(m0 + col0 + u) * ldc + j] : 0.0f;
                     }
-                    for (int sp = 1; sp < ksplit; ++sp) {       // split order: the same sum whichever CTA comes last
-                        float p[CU];
+                    for (int sp = 1; sp < ksplit; sp += SG) {   // split order: the same sum whichever CTA comes last
+                        float p[SG][CU];
 #pragma unroll
-                        for (int u = 0; u < CU; ++u) p[u] = __ldcg(all + ((size_t)sp * N_TILE + col0 + u) * kTcM + r);
+                        for (int g = 0; g < SG; ++g) {          // loads without conditions (a share beyond the last reads the last)
+                            const float *src = all + ((size_t)min(sp + g, ksplit - 1) * N_TILE + col0) * kTcM + r;
 #pragma unroll
-                        for (int u = 0; u < CU; ++u) sum[u] += p[u];
+                            for (int u = 0; u < CU; ++u) p[g][u] = __ldcg(src + (size_t)u * kTcM);
+                        }
+#pragma unroll
+                        for (int g = 0; g < SG; ++g) {
+                            const bool use = sp + g < ksplit;
+#pragma unroll
+                            for (int u = 0; u < CU; ++u) sum[u] = use ? sum[u] + p[g][u] : sum[u];
+                        }
                     }
 #pragma unroll
                     for (int u = 0; u < CU; ++u) {
@@ -416,12 +477,65 @@ spmm_tc_kernel(const uint8_t *__restrict__ dense, int64_t kpad, const int32_t *_
                 if (threadIdx.x == 0) counters[tile_id] = 0u;   // ready for the next product
             }
         }
+        TCL(6, 0);
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     }
     __syncthreads();
+    TCL(7, 0);
     if (warp == kTcEWarps) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem));
+    }
+}
+
+// ---- the shares of k added by a kernel of their own (grids of one wave) -------------------------------------------
+// grid (row blocks, m tiles, groups of 8 dense columns), 128 threads = the W rows of the block.  Same sums in the same
+// order as the last CTA of a tile forms them in spmm_tc_kernel.
+__global__ void __launch_bounds__(128)
+tc_fixup_kernel(const float *__restrict__ partial, int ksplit, int n_tile, const int32_t *__restrict__ row_ptr, int n, int m,
+                float *__restrict__ c, int ldc, float beta, int red, const uint32_t *__restrict__ flag, uint32_t call_id) {
+    constexpr int CU = 8, SG = 3;
+    asm volatile("griddepcontrol.wait;" ::: "memory");         // launched programmatically dependent on the contraction
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    if (__ldcg(flag) == call_id) return;
+    const int r = threadIdx.x, j = blockIdx.x * kTcM + r, m0 = blockIdx.y * n_tile, col0 = blockIdx.z * CU;
+    if (m0 + col0 >= m) return;
+    const size_t tile_id = (size_t)blockIdx.y * gridDim.x + blockIdx.x;
+    const float *all = partial + tile_id * ksplit * (size_t)n_tile * kTcM;
+    const bool have = j < n;
+    const int len = have ? row_ptr[j + 1] - row_ptr[j] : 0;
+    const bool touch = have && !(len == 0 && beta == 1.0f);
+    float sum[CU], v[CU];
+#pragma unroll
+    for (int u = 0; u < CU; ++u) {
+        sum[u] = __ldcg(all + (size_t)(col0 + u) * kTcM + r);
+        v[u] = (touch && !red && m0 + col0 + u < m) ? c[(size_t)(m0 + col0 + u) * ldc + j] : 0.0f;
+    }
+    for (int sp = 1; sp < ksplit; sp += SG) {
+        float p[SG][CU];
+#pragma unroll
+        for (int g = 0; g < SG; ++g) {
+            const float *src = all + ((size_t)min(sp + g, ksplit - 1) * n_tile + col0) * kTcM + r;
+#pragma unroll
+            for (int u = 0; u < CU; ++u) p[g][u] = __ldcg(src + (size_t)u * kTcM);
+        }
+#pragma unroll
+        for (int g = 0; g < SG; ++g) {
+            const bool use = sp + g < ksplit;
+#pragma unroll
+            for (int u = 0; u < CU; ++u) sum[u] = use ? sum[u] + p[g][u] : sum[u];
+        }
+    }
+#pragma unroll
+    for (int u = 0; u < CU; ++u) {
+        if (!touch || m0 + col0 + u >= m) continue;
+        if (red) {
+            if (len) asm volatile("red.global.add.f32 [%0], %1;" ::"l"(c + (size_t)(m0 + col0 + u) * ldc + j), "f"(sum[u]) : "memory");
+            continue;
+        }
+        float cv = v[u];
+        if (beta != 1.0f) cv *= beta;
+        c[(size_t)(m0 + col0 + u) * ldc + j] = len ? cv + sum[u] : cv;
     }
 }
 
@@ -432,6 +546,7 @@ __global__ void __launch_bounds__(256)
 tc_fallback_kernel(const uint32_t *__restrict__ flag, uint32_t call_id, const int32_t *__restrict__ row_ptr,
                    const int32_t *__restrict__ col, const uint8_t *__restrict__ code, const float *__restrict__ table, int T,
                    const float *__restrict__ a, int lda, float *__restrict__ c, int ldc, int n, int m, float alpha, float beta) {
+    asm volatile("griddepcontrol.wait;" ::: "memory");         // launched programmatically dependent on the contraction
     if (*flag != call_id) return;
     const int lane = threadIdx.x & 31;
     for (int j = blockIdx.x * 8 + (threadIdx.x >> 5); j < n; j += gridDim.x * 8) {
@@ -450,6 +565,51 @@ tc_fallback_kernel(const uint32_t *__restrict__ flag, uint32_t call_id, const in
     }
 }
 
+// Programmatic dependent launch: the kernel may be set up while the one before it in the stream drains; it reads what
+// that kernel wrote only after its own griddepcontrol.wait.
+template <typename... KArgs, typename... Args>
+cudaError_t launch_dependent(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+    g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
+    return e;
+}
+
+#ifdef EXP_TC_TIMELINE
+static int g_tcl_ctas = 0;
+static void dump_tc_timeline() {
+    static unsigned long long h[4096 * 8];
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(h, g_tc_timeline, sizeof(h));
+    const int n = std::min(g_tcl_ctas, 4096);
+    unsigned long long t0 = ~0ull, t7 = 0;
+    for (int i = 0; i < n; ++i) { t0 = std::min(t0, h[i * 8]); t7 = std::max(t7, h[i * 8 + 7]); }
+    const char *names[8] = {"start (after the first CTA)", "wait for the split kernel", "tensor memory + barrier", "first operands ready",
+                            "k loop", "partial tile + counter", "fix-up / direct epilogue", "exit barrier"};
+    fprintf(stderr, "[tc timeline] %d CTAs, first start to last end %.1f us\n", n, (t7 - t0) * 1e-3);
+    for (int p = 0; p < 8; ++p) {
+        double avg = 0, mx = 0; int cnt = 0;
+        for (int i = 0; i < n; ++i) {
+            const unsigned long long a = p == 0 ? t0 : h[i * 8 + p - 1], b = h[i * 8 + p];
+            if (p == 5 && b == 0) continue;
+            const unsigned long long a2 = (p == 6 && h[i * 8 + 5] == 0) ? h[i * 8 + 4] : a;
+            if (b < a2) continue;
+            const double d = (b - a2) * 1e-3; avg += d; mx = std::max(mx, d); ++cnt;
+        }
+        fprintf(stderr, "[tc timeline] %-30s avg %7.2f us  max %7.2f us (%d CTAs)\n", names[p], cnt ? avg / cnt : 0.0, mx, cnt);
+    }
+}
+#endif
+
 template <int N_TILE, int STAGES>
 int launch_tc(sblas_b200_matrix *mat, const float *xh, const float *xl, int nkb, int m, float *d_c, int ldc, float alpha, float beta,
               uint32_t *flag, uint32_t call_id, int ksplit, float *partial, uint32_t *counters, int red, cudaStream_t stream) {
@@ -461,9 +621,14 @@ int launch_tc(sblas_b200_matrix *mat, const float *xh, const float *xl, int nkb,
         configured = true;
     }
     const dim3 grid((mat->n + kTcM - 1) / kTcM, (m + N_TILE - 1) / N_TILE, ksplit);
-    SB_LAUNCH((spmm_tc_kernel<N_TILE, STAGES>), grid, kTcThreads, smem, stream, mat->d_dense_code, mat->dense_kpad, mat->d_row_ptr,
-              mat->d_table, mat->T, alpha, xh, xl, nkb, mat->n, m, d_c, ldc, beta, flag, call_id, ksplit, partial, counters, red,
-              getenv("SBLAS_B200_TC_DBG") ? atoi(getenv("SBLAS_B200_TC_DBG")) : 0);
+    const int dbg = getenv("SBLAS_B200_TC_DBG") ? atoi(getenv("SBLAS_B200_TC_DBG")) : 0;
+#ifdef EXP_TC_TIMELINE
+    { static bool reg = false; if (!reg) { atexit(dump_tc_timeline); reg = true; } g_tcl_ctas = grid.x * grid.y * grid.z; }
+#endif
+    SB_CUDA(launch_dependent(spmm_tc_kernel<N_TILE, STAGES>, grid, dim3(kTcThreads), smem, stream, (const uint8_t *)mat->d_dense_code,
+                             (int64_t)mat->dense_kpad, (const int32_t *)mat->d_row_ptr, (const float *)mat->d_table, (int)mat->T, alpha,
+                             xh, xl, nkb, (int)mat->n, m, d_c, ldc, beta, (const uint32_t *)flag, call_id, ksplit, partial, counters,
+                             red, dbg));
     return SBLAS_B200_OK;
 }
 
@@ -499,8 +664,10 @@ static int tc_plan(const sblas_b200_matrix *mat, int m, float alpha, int *ksplit
         if (m < 32) return 0;
         const double t_tile = 12.0 + (double)mat->nnz * ((m + 31) / 32) / 1.69e5;
         const double t_step = n_tile == 64 ? 0.42 : (n_tile == 128 ? 0.56 : 0.92);
+        // fixed part (three or four dependent launches, set-up, pipeline fill, partial tiles): 16 / 19 / 23 us measured at
+        // N = 64 / 128 / 256 with the shares added by tc_fixup_kernel; 8 us more when the last CTA of a tile adds them
         const int64_t waves = ((int64_t)tiles * ksplit + sms - 1) / sms;
-        const double t_tc = 24.0 + (double)waves * ((nkb + ksplit - 1) / ksplit) * t_step + (ksplit > 1 ? 8.0 : 0.0);
+        const double t_tc = 14.0 + 0.035 * n_tile + (double)waves * ((nkb + ksplit - 1) / ksplit) * t_step + ((ksplit > 1 && waves > 1) ? 8.0 : 0.0);
         if (t_tc > 0.9 * t_tile) return 0;
     }
     return n_tile;
@@ -549,7 +716,8 @@ int run_spmm_tc(sblas_b200_matrix *mat, const float *d_a, int m, int lda, float 
     uint32_t *flag = reinterpret_cast<uint32_t *>(ws), *counters = reinterpret_cast<uint32_t *>(ws + 256);
     float *xh = reinterpret_cast<float *>(ws + head_pad), *xl = xh + x_elems, *partial = xl + x_elems;
     const uint32_t call_id = ++mat->tc_calls ? mat->tc_calls : ++mat->tc_calls;     // never 0
-    SB_LAUNCH(tc_split_x_kernel, dim3(nkb, mtiles), 256, 0, stream, d_a, m, mat->k, lda, n_tile, nkb, xh, xl, flag, call_id);
+    const int vec = (lda % 4 == 0 && (reinterpret_cast<uintptr_t>(d_a) & 15) == 0) ? 1 : 0;
+    SB_LAUNCH(tc_split_x_kernel, dim3(nkb, mtiles, n_tile * 8 / 256), 256, 0, stream, d_a, m, mat->k, lda, n_tile, nkb, xh, xl, flag, call_id, vec);
     {
         struct Timer {                                          // event pair around the dominant kernel when profiling
             sblas_b200_matrix *mat; cudaStream_t st; cudaEvent_t a = nullptr, b = nullptr;
@@ -563,13 +731,19 @@ int run_spmm_tc(sblas_b200_matrix *mat, const float *d_a, int m, int lda, float 
         // one code byte per ELEMENT of W is what this kernel reads
         note_product(mat, name, m, (double)mat->n * (double)mat->dense_kpad / (double)mat->nnz, (int64_t)4 * (mat->n + 1));
         int rc;
-        if (n_tile == 64) rc = launch_tc<64, 8>(mat, xh, xl, nkb, m, d_c, ldc, alpha, beta, flag, call_id, ksplit, partial, counters, red, stream);
-        else if (n_tile == 128) rc = launch_tc<128, 6>(mat, xh, xl, nkb, m, d_c, ldc, alpha, beta, flag, call_id, ksplit, partial, counters, red, stream);
-        else rc = launch_tc<256, 3>(mat, xh, xl, nkb, m, d_c, ldc, alpha, beta, flag, call_id, ksplit, partial, counters, red, stream);
+        // one wave of CTAs (small matrices, slabs of a sharded one): the shares are added by a kernel of their own
+        const bool own_fixup = ksplit > 1 && (int64_t)tiles * ksplit <= sms && !(getenv("SBLAS_B200_TC_FIXUP") && atoi(getenv("SBLAS_B200_TC_FIXUP")) == 0);
+        uint32_t *cnt = own_fixup ? nullptr : counters;
+        if (n_tile == 64) rc = launch_tc<64, 8>(mat, xh, xl, nkb, m, d_c, ldc, alpha, beta, flag, call_id, ksplit, partial, cnt, red, stream);
+        else if (n_tile == 128) rc = launch_tc<128, 6>(mat, xh, xl, nkb, m, d_c, ldc, alpha, beta, flag, call_id, ksplit, partial, cnt, red, stream);
+        else rc = launch_tc<256, 3>(mat, xh, xl, nkb, m, d_c, ldc, alpha, beta, flag, call_id, ksplit, partial, cnt, red, stream);
         if (rc != SBLAS_B200_OK) return rc;
+        if (own_fixup)
+            SB_CUDA(launch_dependent(tc_fixup_kernel, dim3((mat->n + kTcM - 1) / kTcM, mtiles, n_tile / 8), dim3(kTcM), 0, stream, partial, ksplit,
+                                     n_tile, mat->d_row_ptr, mat->n, m, d_c, ldc, beta, red, flag, call_id));
     }
-    SB_LAUNCH(tc_fallback_kernel, sms, 256, 0, stream, flag, call_id, mat->d_row_ptr, mat->d_col, mat->d_code, mat->d_table, mat->T, d_a, lda,
-              d_c, ldc, mat->n, m, alpha, beta);
+    SB_CUDA(launch_dependent(tc_fallback_kernel, dim3(sms), dim3(256), 0, stream, flag, call_id, mat->d_row_ptr, mat->d_col, mat->d_code,
+                             mat->d_table, mat->T, d_a, lda, d_c, ldc, mat->n, m, alpha, beta));
     SB_CHECK_LAUNCH();
     return SBLAS_B200_OK;
 }

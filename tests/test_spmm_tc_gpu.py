@@ -79,6 +79,31 @@ def test_tensor_core_spmm_split_k_is_deterministic_and_equal_in_tolerance():
     dev.free()
 
 
+def test_tensor_core_spmm_shares_added_by_their_own_kernel_or_by_the_last_cta_give_the_same_bits():
+    # grids of one wave add the shares of k with tc_fixup_kernel, larger ones inside the contraction (the last CTA of a
+    # tile); SBLAS_B200_TC_FIXUP=0 forces the latter.  Same sums in the same order.
+    n, k = 700, 2048                                           # 6 row blocks x m tiles x 4 shares: one wave up to m = 256 x 4
+    codes = gen.codes_bernoulli(n, k, 0.3, seed=77)
+    codes[9, :] = 255
+    s = O.copyform(codes, n, k, k, gen.codebook(255, 1), 255, True)
+    dev = sb.DeviceMatrix.upload(s.pos, s.code, s.table, s.T, s.block_bounds, s.block_index_bounds, s.rows, s.cols)
+    for m, alpha, beta, pc in ((40, 1.0, 1.0, 0), (128, 1.7, 0.0, 3), (300, 0.9, 2.0, 1)):
+        own, _, _ = _check(dev, s, m, alpha, beta, 0, pc, seed=m)
+        assert int(dev.last_product()["kernel"].split(">x")[1]) > 1
+        inside, _, _ = _env("SBLAS_B200_TC_FIXUP", "0", lambda: _check(dev, s, m, alpha, beta, 0, pc, seed=m))
+        assert_bits_equal(own, inside, f"m={m}: shares added by tc_fixup_kernel vs by the last CTA")
+    # non-finite x with the separate kernel: the fallback computes the product, nothing of the tensor-core pass is stored
+    a = gen.dense_uniform((64, k), 5)
+    a[3, 17] = np.inf
+    c0 = gen.dense_uniform((64, n), 6)
+    got = _env("SBLAS_B200_SPMM_TC", "1", lambda: dev.addmatmat_host(a, 64, k, c0.copy(), n, 1.0, 1.0))
+    want = _env("SBLAS_B200_SPMM_TC", "0", lambda: dev.addmatmat_host(a, 64, k, c0.copy(), n, 1.0, 1.0))
+    fin = np.isfinite(want)
+    assert np.array_equal(np.isfinite(got), fin)
+    np.testing.assert_allclose(got[fin], want[fin], rtol=1e-4, atol=1e-4)
+    dev.free()
+
+
 def test_tensor_core_spmm_never_lets_x_through_where_no_entry_is():
     n, k, m = 256, 512, 40
     codes = gen.codes_bernoulli(n, k, 0.25, seed=71)

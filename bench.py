@@ -568,6 +568,8 @@ def measure(name, args, cx):
             tc_ach = tc_flops / (kern_us * 1e-6) / 1e12
             roof.update({"bound": "tensor", "achieved": tc_ach, "peak": tc_peak, "unit": "TFLOP/s", "frac": tc_ach / tc_peak,
                          "executed_tf32_flops": tc_flops,
+                         "kernel_us_covers": "tc_split_x_kernel + spmm_tc_kernel (+ tc_fixup_kernel) + tc_fallback_kernel: chained by "
+                                             "programmatic dependent launch, timed as one (an event between them undoes the overlap)",
                          "peak_source": "tensor: nominal dense TF32 = half of the 2250 TFLOP/s bf16 figure (B200_PROFILING.md); "
                                         "MEASURED_PEAKS.json has cuBLAS bf16 only: %s TFLOP/s burst, i.e. %.0f for TF32; hbm: %s"
                                         % (cx.bf16_measured, (cx.bf16_measured or 0) / 2, peak_src),

@@ -149,14 +149,14 @@ __device__ __forceinline__ void tmem_ld_sum(uint32_t taddr, float (&v)[32]) {
 
 #ifdef EXP_TC_TIMELINE
 // experiment build only (tools/build_variant.sh): phase stamps of every CTA of the last contraction, dumped at exit
-__device__ unsigned long long g_tc_timeline[4096 * 8];
+__device__ unsigned long long g_tc_timeline[4096 * 16];
 __device__ __forceinline__ unsigned long long tc_gtime() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     return t;
 }
 #define TCL(p, tid) do { if (threadIdx.x == (tid)) { const unsigned b_ = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x; \
-                         if (b_ < 4096) g_tc_timeline[b_ * 8 + (p)] = tc_gtime(); } } while (0)
+                         if (b_ < 4096) g_tc_timeline[b_ * 16 + (p)] = tc_gtime(); } } while (0)
 #else
 #define TCL(p, tid) do { } while (0)
 #endif
@@ -225,7 +225,8 @@ spmm_tc_kernel(const uint8_t *__restrict__ dense, int64_t kpad, const int32_t *_
     float *tab_s = reinterpret_cast<float *>(sm + XS * STAGE_BYTES);    // [256][kTcTabCopies]: entry c for lane l at c * 16 + (l & 15)
     uint64_t *full_x = reinterpret_cast<uint64_t *>(tab_s + 256 * kTcTabCopies), *empty_x = full_x + XS, *full_w = empty_x + XS,
              *empty_w = full_w + WS, *acc_full = empty_w + WS;
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_full + 1);
+    uint64_t *fix_bar = acc_full + 1;                           // [2]: partial tiles of other shares have arrived (last CTA of a tile)
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_full + 3);
     uint32_t *last_slot = tmem_slot + 1;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -256,6 +257,8 @@ spmm_tc_kernel(const uint8_t *__restrict__ dense, int64_t kpad, const int32_t *_
         for (int s = 0; s < XS; ++s) { mbar_init(&full_x[s], 1); mbar_init(&empty_x[s], 1); }
         for (int s = 0; s < WS; ++s) { mbar_init(&full_w[s], 4); mbar_init(&empty_w[s], 1); }
         mbar_init(acc_full, 1);
+        mbar_init(&fix_bar[0], 1);
+        mbar_init(&fix_bar[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     // Launched programmatically dependent on tc_split_x_kernel: the set-up and the expansion of the first W operands run
@@ -410,67 +413,133 @@ spmm_tc_kernel(const uint8_t *__restrict__ dense, int64_t kpad, const int32_t *_
                 }
             }
         } else {
-            // partial tile [N_TILE][128] of this split, then the last CTA of the tile adds the splits in order
-            const size_t tile_id = (size_t)blockIdx.y * gridDim.x + blockIdx.x;
-            float *mine = partial + (tile_id * ksplit + split) * (size_t)N_TILE * kTcM;
-            for (int col0 = 32 * set; col0 < N_TILE && m0 + col0 < m; col0 += 64) {
-                float acc[32];
-                if (steps > 0) tmem_ld_sum<NACC, N_TILE>(t_lane + col0, acc);
-                else {
-#pragma unroll
-                    for (int t = 0; t < 32; ++t) acc[t] = 0.0f;
-                }
-#pragma unroll
-                for (int t = 0; t < 32; ++t) mine[(size_t)(col0 + t) * kTcM + r] = acc[t];
-            }
+            // partial tile [N_TILE][128] of this share; the last CTA of a tile to get here adds the shares in share order.
             // counters == nullptr: the whole grid is one wave of CTAs and tc_fixup_kernel adds the shares with every SM (here
             // the last CTA of each tile would do it alone, all of them at the same time at the end of the only wave)
+            const size_t tile_id = (size_t)blockIdx.y * gridDim.x + blockIdx.x;
+            float *mine = partial + (tile_id * ksplit + split) * (size_t)N_TILE * kTcM;
+            // every other share already there (the usual case in grids of several waves: a tile's shares run in different
+            // waves): this CTA is the last one and keeps its share in tensor memory instead of writing it out
+            bool early = false;
             if (counters != nullptr) {
-                __threadfence();
+                if (threadIdx.x == 0) {
+                    uint32_t seen;
+                    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(counters + tile_id) : "memory");
+                    *last_slot = seen == (uint32_t)(ksplit - 1) ? 2u : 0u;
+                }
                 asm volatile("bar.sync 1, 256;" ::: "memory");  // the eight epilogue warps
-                if (threadIdx.x == 0) *last_slot = atomicAdd(&counters[tile_id], 1u) == (uint32_t)(ksplit - 1) ? 1u : 0u;
-                asm volatile("bar.sync 1, 256;" ::: "memory");
+                early = *last_slot == 2u;
+            }
+            if (!early) {
+                for (int col0 = 32 * set; col0 < N_TILE && m0 + col0 < m; col0 += 64) {
+                    float acc[32];
+                    if (steps > 0) tmem_ld_sum<NACC, N_TILE>(t_lane + col0, acc);
+                    else {
+#pragma unroll
+                        for (int t = 0; t < 32; ++t) acc[t] = 0.0f;
+                    }
+#pragma unroll
+                    for (int t = 0; t < 32; ++t) mine[(size_t)(col0 + t) * kTcM + r] = acc[t];
+                }
+                if (counters != nullptr) {
+                    __threadfence();
+                    asm volatile("bar.sync 1, 256;" ::: "memory");
+                    if (threadIdx.x == 0) *last_slot = atomicAdd(&counters[tile_id], 1u) == (uint32_t)(ksplit - 1) ? 1u : 0u;
+                    asm volatile("bar.sync 1, 256;" ::: "memory");
+                }
             }
             TCL(5, 0);
             if (counters != nullptr && *last_slot) {
+                // The other shares' partial tiles come in by bulk copy, 64 dense columns (32 KB per share) at a time, into the
+                // idle X ring -- every MMA has completed, so has every copy of the X producer -- and are added from shared
+                // memory, this CTA's own share from tensor memory at its place in the order (share 0, 1, 2, ...: the same sum
+                // whichever CTA comes last).  Rounds of (column group, HS shares) alternate between the two halves of the
+                // ring: the copies of round i + 1 travel while round i is added; the C tile is prefetched into L2 up front.
+                // (Plain loads, 80 in flight per thread, took 27 us per tile of N = 256 here and the same copies one round at a
+                // time 32 us: every step of a round is a latency of its own, profiles/r02_spmm_tc.md.)
                 __threadfence();
+                TCL(8, 0);
+                constexpr int GC = 64, SLOT = GC * kTcM * 4, HS = XS * STAGE_BYTES / SLOT / 2;
+                static_assert(HS >= 1, "each half of the X ring holds at least one 32 KB slot");
                 const float *all = partial + tile_id * ksplit * (size_t)N_TILE * kTcM;
-                // 16 columns per step and three more shares at a time: up to 80 loads of a thread travel together (the loop
-                // is a chain of L2 round trips otherwise: cfg2 spent half of its 43 us here with 8 columns and one share
-                // at a time, profiles/r02_spmm_tc.md).  The order of the additions stays share 0, 1, 2, ...
-                constexpr int CU = 16, SG = 3;
-                for (int col0 = CU * set; col0 < N_TILE && m0 + col0 < m; col0 += 2 * CU) {
-                    float sum[CU], v[CU];
+                if (!red && (ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(c) & 15) == 0) {
+                    const int t = threadIdx.x;                  // dense column m0 + t: 512 contiguous bytes of C
+                    if (t < N_TILE && m0 + t < m && j0 + kTcM <= n)
+                        asm volatile("cp.async.bulk.prefetch.L2.global [%0], 512;" ::"l"(c + (size_t)(m0 + t) * ldc + j0) : "memory");
+                }
+                // a round = one column group x up to HS of the other shares (o = 0 .. ksplit - 2, share o or o + 1 past this
+                // CTA's own); the own share is added in the round its place in the order falls into
+                const int nothers = ksplit - 1, nbatch = (nothers + HS - 1) / HS;
+                const int ngroups = (min(N_TILE, m - m0) + GC - 1) / GC, rounds = ngroups * nbatch;
+                auto share_of = [&](int o) { return o < split ? o : o + 1; };
+                auto issue = [&](int rd) {                      // thread 0: the copies of round rd into half rd & 1
+                    const int g0 = (rd / nbatch) * GC, o_lo = (rd % nbatch) * HS, o_hi = min(o_lo + HS, nothers);
+                    uint64_t *bar = &fix_bar[rd & 1];
+                    uint8_t *half = sm + (size_t)(rd & 1) * HS * SLOT;
+                    mbar_expect_tx(bar, (uint32_t)(o_hi - o_lo) * SLOT);
+                    for (int o = o_lo; o < o_hi; ++o)
+                        bulk_g2s(half + (o - o_lo) * SLOT, all + ((size_t)share_of(o) * N_TILE + g0) * kTcM, SLOT, bar);
+                };
+                TCL(13, 0);
+                if (threadIdx.x == 0) {
+                    asm volatile("fence.proxy.async;" ::: "memory");   // written with ordinary stores, read by the bulk copies
+                    TCL(14, 0);
+                    issue(0);
+                }
+                TCL(15, 0);
+                uint32_t used0 = 0u, used1 = 0u;                // completed phases of the two barriers
+                float sum[32], c_old[32];
+                for (int rd = 0; rd < rounds; ++rd) {
+                    const int g0 = (rd / nbatch) * GC, b = rd % nbatch, o_lo = b * HS, o_hi = min(o_lo + HS, nothers);
+                    const int sb = b == 0 ? 0 : share_of(o_lo), se = b == nbatch - 1 ? ksplit : share_of(o_hi);   // shares sb .. se - 1
+                    const int col0 = g0 + 32 * set;              // this thread: row r, columns col0 .. col0 + 31
+                    if (threadIdx.x == 0 && rd + 1 < rounds) issue(rd + 1);   // its half was released by the barrier that ended round rd - 1
+                    if (b == 0) {
 #pragma unroll
-                    for (int u = 0; u < CU; ++u) {
-                        sum[u] = __ldcg(all + (size_t)(col0 + u) * kTcM + r);
-                        v[u] = (touch && !red && m0 + col0 + u < m) ? c[(size_t)(m0 + col0 + u) * ldc + j] : 0.0f;
+                        for (int t = 0; t < 32; ++t)
+                            c_old[t] = (touch && !red && m0 + col0 + t < m) ? c[(size_t)(m0 + col0 + t) * ldc + j] : 0.0f;
+                        if (rd == 0) TCL(9, 0);
                     }
-                    for (int sp = 1; sp < ksplit; sp += SG) {   // split order: the same sum whichever CTA comes last
-                        float p[SG][CU];
+                    if (rd & 1) { mbar_wait_or_trap(&fix_bar[1], used1 & 1u); ++used1; }
+                    else { mbar_wait_or_trap(&fix_bar[0], used0 & 1u); ++used0; }
+                    if (rd == 0) TCL(10, 0);
+                    const uint8_t *half = sm + (size_t)(rd & 1) * HS * SLOT;
+                    for (int sp = sb; sp < se; ++sp) {
+                        float v[32];
+                        if (sp == split) {
+                            if (steps > 0) tmem_ld_sum<NACC, N_TILE>(t_lane + col0, v);
+                            else {
 #pragma unroll
-                        for (int g = 0; g < SG; ++g) {          // loads without conditions (a share beyond the last reads the last)
-                            const float *src = all + ((size_t)min(sp + g, ksplit - 1) * N_TILE + col0) * kTcM + r;
+                                for (int t = 0; t < 32; ++t) v[t] = 0.0f;
+                            }
+                        } else {
+                            const float *sl = reinterpret_cast<const float *>(half + ((sp < split ? sp : sp - 1) - o_lo) * SLOT) + (size_t)(32 * set) * kTcM + r;
 #pragma unroll
-                            for (int u = 0; u < CU; ++u) p[g][u] = __ldcg(src + (size_t)u * kTcM);
+                            for (int t = 0; t < 32; ++t) v[t] = sl[t * kTcM];
                         }
+                        if (sp == 0) {
 #pragma unroll
-                        for (int g = 0; g < SG; ++g) {
-                            const bool use = sp + g < ksplit;
+                            for (int t = 0; t < 32; ++t) sum[t] = v[t];
+                        } else {
 #pragma unroll
-                            for (int u = 0; u < CU; ++u) sum[u] = use ? sum[u] + p[g][u] : sum[u];
+                            for (int t = 0; t < 32; ++t) sum[t] += v[t];
                         }
                     }
+                    if (rd == 0) TCL(11, 0);
+                    asm volatile("bar.sync 1, 256;" ::: "memory");   // this half may be overwritten (by the copies of round rd + 2)
+                    if (b == nbatch - 1) {
 #pragma unroll
-                    for (int u = 0; u < CU; ++u) {
-                        if (!touch || m0 + col0 + u >= m) continue;
-                        if (red) {
-                            if (len) asm volatile("red.global.add.f32 [%0], %1;" ::"l"(c + (size_t)(m0 + col0 + u) * ldc + j), "f"(sum[u]) : "memory");
-                            continue;
+                        for (int t = 0; t < 32; ++t) {
+                            if (!touch || m0 + col0 + t >= m) continue;
+                            if (red) {
+                                if (len) asm volatile("red.global.add.f32 [%0], %1;" ::"l"(c + (size_t)(m0 + col0 + t) * ldc + j), "f"(sum[t]) : "memory");
+                                continue;
+                            }
+                            float cv = c_old[t];
+                            if (beta != 1.0f) cv *= beta;
+                            c[(size_t)(m0 + col0 + t) * ldc + j] = len ? cv + sum[t] : cv;
                         }
-                        float cv = v[u];
-                        if (beta != 1.0f) cv *= beta;
-                        c[(size_t)(m0 + col0 + u) * ldc + j] = len ? cv + sum[u] : cv;
+                        if (rd == nbatch - 1) TCL(12, 0);
                     }
                 }
                 asm volatile("bar.sync 1, 256;" ::: "memory");
@@ -587,25 +656,33 @@ cudaError_t launch_dependent(void (*kernel)(KArgs...), dim3 grid, dim3 block, si
 #ifdef EXP_TC_TIMELINE
 static int g_tcl_ctas = 0;
 static void dump_tc_timeline() {
-    static unsigned long long h[4096 * 8];
+    static unsigned long long h[4096 * 16];
     cudaDeviceSynchronize();
     cudaMemcpyFromSymbol(h, g_tc_timeline, sizeof(h));
     const int n = std::min(g_tcl_ctas, 4096);
     unsigned long long t0 = ~0ull, t7 = 0;
-    for (int i = 0; i < n; ++i) { t0 = std::min(t0, h[i * 8]); t7 = std::max(t7, h[i * 8 + 7]); }
+    for (int i = 0; i < n; ++i) { t0 = std::min(t0, h[i * 16]); t7 = std::max(t7, h[i * 16 + 7]); }
     const char *names[8] = {"start (after the first CTA)", "wait for the split kernel", "tensor memory + barrier", "first operands ready",
                             "k loop", "partial tile + counter", "fix-up / direct epilogue", "exit barrier"};
     fprintf(stderr, "[tc timeline] %d CTAs, first start to last end %.1f us\n", n, (t7 - t0) * 1e-3);
     for (int p = 0; p < 8; ++p) {
         double avg = 0, mx = 0; int cnt = 0;
         for (int i = 0; i < n; ++i) {
-            const unsigned long long a = p == 0 ? t0 : h[i * 8 + p - 1], b = h[i * 8 + p];
+            const unsigned long long a = p == 0 ? t0 : h[i * 16 + p - 1], b = h[i * 16 + p];
             if (p == 5 && b == 0) continue;
-            const unsigned long long a2 = (p == 6 && h[i * 8 + 5] == 0) ? h[i * 8 + 4] : a;
+            const unsigned long long a2 = (p == 6 && h[i * 16 + 5] == 0) ? h[i * 16 + 4] : a;
             if (b < a2) continue;
             const double d = (b - a2) * 1e-3; avg += d; mx = std::max(mx, d); ++cnt;
         }
         fprintf(stderr, "[tc timeline] %-30s avg %7.2f us  max %7.2f us (%d CTAs)\n", names[p], cnt ? avg / cnt : 0.0, mx, cnt);
+    }
+    // inside the last CTA's addition of the shares (first column group): stamps 8..12 relative to stamp 5
+    const char *fx[8] = {"fence", "C loads issued", "partials arrived", "added", "stored", "prefetch + index math", "proxy fence", "copies of round 0 issued"};
+    for (int p = 8; p < 16; ++p) {
+        double avg = 0; int cnt = 0;
+        for (int i = 0; i < n; ++i)
+            if (h[i * 16 + p] > h[i * 16 + 5] && h[i * 16 + p] < h[i * 16 + 6] + 1) { avg += (h[i * 16 + p] - h[i * 16 + 5]) * 1e-3; ++cnt; }
+        fprintf(stderr, "[tc timeline]   shares, first group: %-18s at %7.2f us (%d CTAs)\n", fx[p - 8], cnt ? avg / cnt : 0.0, cnt);
     }
 }
 #endif
@@ -613,7 +690,7 @@ static void dump_tc_timeline() {
 template <int N_TILE, int STAGES>
 int launch_tc(sblas_b200_matrix *mat, const float *xh, const float *xl, int nkb, int m, float *d_c, int ldc, float alpha, float beta,
               uint32_t *flag, uint32_t call_id, int ksplit, float *partial, uint32_t *counters, int red, cudaStream_t stream) {
-    constexpr size_t smem = (size_t)STAGES * (2 * N_TILE * 128) + 256 * kTcTabCopies * 4 + (2 * STAGES + 2 * kTcWStages + 1) * 8 + 16 + 1024;
+    constexpr size_t smem = (size_t)STAGES * (2 * N_TILE * 128) + 256 * kTcTabCopies * 4 + (2 * STAGES + 2 * kTcWStages + 3) * 8 + 16 + 1024;
     static bool configured_on[64] = {false};
     bool &configured = configured_on[mat->device & 63];
     if (!configured) {
@@ -717,15 +794,18 @@ int run_spmm_tc(sblas_b200_matrix *mat, const float *d_a, int m, int lda, float 
     float *xh = reinterpret_cast<float *>(ws + head_pad), *xl = xh + x_elems, *partial = xl + x_elems;
     const uint32_t call_id = ++mat->tc_calls ? mat->tc_calls : ++mat->tc_calls;     // never 0
     const int vec = (lda % 4 == 0 && (reinterpret_cast<uintptr_t>(d_a) & 15) == 0) ? 1 : 0;
+    // event pair around the product's kernels when profiling: the split kernel, the contraction and what follows are
+    // chained by programmatic dependent launches and overlap, an event between them would undo that (and did: the
+    // contraction alone then measured longer than the whole product)
+    struct Timer {
+        sblas_b200_matrix *mat; cudaStream_t st; cudaEvent_t a = nullptr, b = nullptr;
+        Timer(sblas_b200_matrix *m_, cudaStream_t s_) : mat(m_), st(s_) {
+            if (mat->profiling) { cudaEventCreate(&a); cudaEventCreate(&b); cudaEventRecord(a, st); }
+        }
+        ~Timer() { if (a) { cudaEventRecord(b, st); mat->prof_events.push_back(std::make_pair(a, b)); } }
+    } timer(mat, stream);
     SB_LAUNCH(tc_split_x_kernel, dim3(nkb, mtiles, n_tile * 8 / 256), 256, 0, stream, d_a, m, mat->k, lda, n_tile, nkb, xh, xl, flag, call_id, vec);
     {
-        struct Timer {                                          // event pair around the dominant kernel when profiling
-            sblas_b200_matrix *mat; cudaStream_t st; cudaEvent_t a = nullptr, b = nullptr;
-            Timer(sblas_b200_matrix *m_, cudaStream_t s_) : mat(m_), st(s_) {
-                if (mat->profiling) { cudaEventCreate(&a); cudaEventCreate(&b); cudaEventRecord(a, st); }
-            }
-            ~Timer() { if (a) { cudaEventRecord(b, st); mat->prof_events.push_back(std::make_pair(a, b)); } }
-        } timer(mat, stream);
         char name[64];
         snprintf(name, sizeof(name), "spmm_tc<%d>x%d", n_tile, ksplit);
         // one code byte per ELEMENT of W is what this kernel reads

@@ -92,6 +92,15 @@ def test_tensor_core_spmm_shares_added_by_their_own_kernel_or_by_the_last_cta_gi
         assert int(dev.last_product()["kernel"].split(">x")[1]) > 1
         inside, _, _ = _env("SBLAS_B200_TC_FIXUP", "0", lambda: _check(dev, s, m, alpha, beta, 0, pc, seed=m))
         assert_bits_equal(own, inside, f"m={m}: shares added by tc_fixup_kernel vs by the last CTA")
+    # more shares than the last CTA's staging area holds at a time (4 or 6 slots), shares that are not multiples of it
+    for ks in ("7", "13"):
+        def both():
+            own, _, _ = _check(dev, s, 128, 1.3, 1.0, 0, 0, seed=3)
+            inside, _, _ = _env("SBLAS_B200_TC_FIXUP", "0", lambda: _check(dev, s, 128, 1.3, 1.0, 0, 0, seed=3))
+            return own, inside
+        own, inside = _env("SBLAS_B200_TC_KSPLIT", ks, both)
+        assert dev.last_product()["kernel"].endswith("x" + ks), dev.last_product()["kernel"]
+        assert_bits_equal(own, inside, f"{ks} shares: tc_fixup_kernel vs the last CTA")
     # non-finite x with the separate kernel: the fallback computes the product, nothing of the tensor-core pass is stored
     a = gen.dense_uniform((64, k), 5)
     a[3, 17] = np.inf

@@ -580,7 +580,7 @@ def measure(name, args, cx):
         sm_hz = (clk.get("sm_mhz") or 1965.0) * 1e6
         # what actually bounds the kernel on the chip
         if lp["kernel"].startswith("spmm_tc"):
-            roof["onchip"] = {"limiter": "tensor pipe (ncu sm__pipe_tc_cycles_active 86 % on cfg3, profiles/r02_cfg3_full.txt); "
+            roof["onchip"] = {"limiter": "tensor pipe (ncu sm__pipe_tc_cycles_active 90 % on cfg3, 67 % on cfg2: profiles/r02f_cfg{3,2}_full.txt); "
                                          "the CUDA-core form of this product is capped at 25 % of the fp32 peak by the shared-memory pipe"}
         elif lp["kernel"].startswith("spmm_tile"):
             wavefronts = nnz_local * ((m + 31) // 32)                   # 4*m B of X per non-zero through a 128 B/clk/SM pipe

@@ -1,8 +1,8 @@
 #!/bin/bash
 # r02 evidence: ncu --set full captures of the dominant kernels and per-launch time lists (one gpurun call, one GPU).
-OUT=gpurun_out/r02n
+OUT=gpurun_out/${NCU_TAG:-r02n}
 mkdir -p $OUT
-for spec in "cfg3:spmm_tc_kernel:3" "cfg4:spmv_blocked:6" "cfg2:spmm_tile_kernel:3"; do
+for spec in "cfg3:spmm_tc_kernel:3" "cfg4:spmv_blocked:6" "cfg2:spmm_tc_kernel:3"; do
   W=${spec%%:*}; rest=${spec#*:}; K=${rest%%:*}; SKIP=${rest#*:}
   CMD="python bench.py --workload $W --steps 3 --warmup 3 --no-cpu-baseline"
   $CMD > $OUT/plain_$W.log 2>&1 &&

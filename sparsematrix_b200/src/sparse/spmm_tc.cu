@@ -420,8 +420,9 @@ spmm_tc_kernel(const uint8_t *__restrict__ dense, int64_t kpad, const int32_t *_
             float *mine = partial + (tile_id * ksplit + split) * (size_t)N_TILE * kTcM;
             // every other share already there (the usual case in grids of several waves: a tile's shares run in different
             // waves): this CTA is the last one and keeps its share in tensor memory instead of writing it out
+            // (only the highest share looks: it is launched last, and the look costs an L2 round trip)
             bool early = false;
-            if (counters != nullptr) {
+            if (counters != nullptr && split == ksplit - 1) {
                 if (threadIdx.x == 0) {
                     uint32_t seen;
                     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(counters + tile_id) : "memory");

@@ -619,7 +619,10 @@ def measure(name, args, cx):
                       "kernel": lp["kernel"], "spmv_lanes": int(mat.info().spmv_lanes) if mat is not None else None,
                       "long_rows": int(mat.info().long_rows) if mat is not None else None},
             "effective_gbs": bytes_alg * (flops / max(flops_k, 1.0)) / (ms_step * 1e-3) / 1e9,
-            "warm_l2": {"ms_per_step": warm_ms / args.steps, "value": flops / (warm_ms / args.steps * 1e-3) / 1e9},
+            "warm_l2": {"ms_per_step": warm_ms / args.steps, "value": flops / (warm_ms / args.steps * 1e-3) / 1e9,
+                        "note": "products back to back, no flush in between" + (
+                            "; the tensor-core form reaches the board's power cap in this pass (sw_power_cap, 1680 MHz measured): "
+                            "slower than the flushed steps although L2 is warm" if lp["kernel"].startswith("spmm_tc") else "")},
             "roofline": roof,
             "e2e": {"value": flops / (e2e_ms / e2e_steps * 1e-3) / 1e9, "unit": "GFLOP/s",
                     "h2d_bytes_per_step": int(4 * m * (k + n)), "d2h_bytes_per_step": int(4 * m * n),

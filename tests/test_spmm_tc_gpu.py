@@ -165,19 +165,22 @@ def test_tensor_core_spmm_into_a_registered_peer_range_adds_with_reductions():
     a = torch.from_numpy(gen.dense_uniform((m, k), 1)).cuda()
     c0 = gen.dense_uniform((m, n), 2); c0[3, 7] = -0.0
     L = sb.lib()
-    for beta in (1.0, 0.5):
-        want = torch.from_numpy(c0.copy()).cuda()
-        _env("SBLAS_B200_SPMM_TC", "1", lambda: dev.addmatmat_dev(a, m, k, want, n, 1.3, beta))
-        assert dev.last_product()["kernel"].startswith("spmm_tc")
-        buf = torch.from_numpy(c0.copy()).cuda()
-        assert L.sblas_b200_peer_register(C.c_void_p(buf.data_ptr()), buf.numel() * 4) == _capi.OK
-        try:
-            _env("SBLAS_B200_SPMM_TC", "1", lambda: dev.addmatmat_dev(a, m, k, buf, n, 1.3, beta))
-            torch.cuda.synchronize()
-        finally:
-            assert L.sblas_b200_peer_unregister(C.c_void_p(buf.data_ptr())) == _capi.OK
-        assert dev.last_product()["kernel"].startswith("spmm_tc")
-        assert_bits_equal(buf.cpu().numpy(), want.cpu().numpy(), f"peer range beta={beta}")
+    # the shares of k added by tc_fixup_kernel ("1": the grid is one wave) and by the last CTA of a tile ("0"): both epilogues
+    for fixup in ("1", "0"):
+        for beta in (1.0, 0.5):
+            want = torch.from_numpy(c0.copy()).cuda()
+            _env("SBLAS_B200_TC_FIXUP", fixup, lambda: _env("SBLAS_B200_SPMM_TC", "1", lambda: dev.addmatmat_dev(a, m, k, want, n, 1.3, beta)))
+            assert dev.last_product()["kernel"].startswith("spmm_tc")
+            assert int(dev.last_product()["kernel"].split(">x")[1]) > 1
+            buf = torch.from_numpy(c0.copy()).cuda()
+            assert L.sblas_b200_peer_register(C.c_void_p(buf.data_ptr()), buf.numel() * 4) == _capi.OK
+            try:
+                _env("SBLAS_B200_TC_FIXUP", fixup, lambda: _env("SBLAS_B200_SPMM_TC", "1", lambda: dev.addmatmat_dev(a, m, k, buf, n, 1.3, beta)))
+                torch.cuda.synchronize()
+            finally:
+                assert L.sblas_b200_peer_unregister(C.c_void_p(buf.data_ptr())) == _capi.OK
+            assert dev.last_product()["kernel"].startswith("spmm_tc")
+            assert_bits_equal(buf.cpu().numpy(), want.cpu().numpy(), f"peer range beta={beta} fixup={fixup}")
     dev.free()
 
 

@@ -362,6 +362,11 @@ static int run_spmv(sblas_b200_matrix *mat, const float *x, float *y, float alph
     // matrices with >= 3/16 of their elements stored: one byte per element, x in registers (spmv_dense.cu)
     const int drc = staged ? 1 : run_spmv_dense(mat, x, y, alpha, beta, stream);
     if (drc <= 0) return drc;
+    // large matrices in between: straight from the reference's own byte streams, x read front to back (spmv_native.cu)
+    if (!staged) {
+        const int nrc = run_spmv_native(mat, x, y, alpha, beta, stream);
+        if (nrc <= 0) return nrc;
+    }
     // the length-sorted copy visits rows in sorted order: into peer memory its row sums would travel as scattered
     // 4-byte packets (8 GPUs into one: 3.3 ms instead of 0.6) -- they are formed locally and added out in row order
     if (!staged && mat->d_row_order && is_peer_pointer(y)) return run_spmv_sorted_to_peer(mat, x, y, alpha, beta, stream);

@@ -452,6 +452,9 @@ static void release(sblas_b200_matrix *mat) {
     cudaFree(mat->d_ws); cudaFree(mat->d_partial); cudaFree(mat->d_host_a); cudaFree(mat->d_host_c);
     cudaFree(mat->d_host_p); cudaFree(mat->d_dense_code); cudaFree(mat->d_peer_y);
     cudaFree(mat->d_tc_ws);
+    cudaFree(mat->native.d_pos); cudaFree(mat->native.d_code); cudaFree(mat->native.d_seg_begin); cudaFree(mat->native.d_seg_end);
+    cudaFree(mat->native.d_seg_pos0); cudaFree(mat->native.d_panel_seg_first); cudaFree(mat->native.d_slot_panel);
+    cudaFree(mat->native.d_partial);
     cudaFree(mat->blocked.d_lcol); cudaFree(mat->blocked.d_lrow); cudaFree(mat->blocked.d_code);
     cudaFree(mat->blocked.d_seg_ptr); cudaFree(mat->blocked.d_cb_start); cudaFree(mat->blocked.d_prod);
     if (mat->stream) cudaStreamDestroy(mat->stream);
@@ -469,14 +472,56 @@ struct UploadScratch {
             *panel_col_off = nullptr, *seg_hist = nullptr, *row_len = nullptr;
     uint32_t *seg_pos0 = nullptr;
     unsigned long long *fillers = nullptr;
+    int32_t *hist_max = nullptr;                       // most entries of one column inside one segment
     ~UploadScratch() {
         cudaFree(pos); cudaFree(code); cudaFree(seg_begin); cudaFree(seg_end); cudaFree(seg_panel);
         cudaFree(panel_seg_first); cudaFree(panel_col_off); cudaFree(seg_hist); cudaFree(row_len);
-        cudaFree(seg_pos0); cudaFree(fillers);
+        cudaFree(seg_pos0); cudaFree(fillers); cudaFree(hist_max);
     }
 };
 
 // pos_bytes = sizeof(PosIndex_t): 1 for the reference's instantiation, 2 for SparseMatrix<uint16, uint8, float>
+// the largest per-segment column count (seg_hist before panel_bin_scan_kernel turns it into offsets)
+__global__ void __launch_bounds__(256)
+seg_hist_max_kernel(const int32_t *__restrict__ seg_hist, size_t count, int32_t *__restrict__ out) {
+    int32_t m = 0;
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < count; i += (size_t)gridDim.x * 256) m = max(m, seg_hist[i]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0 && m > 0) atomicMax(out, m);
+}
+
+// Keep the slab's streams and segment table in the handle for src/sparse/spmv_native.cu instead of freeing
+// them with the rest of the upload scratch.  One-byte positions only.  Opt-in (SBLAS_B200_KEEP_NATIVE=1): the native kernel
+// is measured slower than the CSR kernels everywhere (run_spmv_native), so the 2 bytes per entry are not spent by default.
+static int keep_native_streams(sblas_b200_matrix *mat, UploadScratch &sc, int nseg, int np, int pos_bytes,
+                               const std::vector<int32_t> &panel_col_off) {
+    const char *env = getenv("SBLAS_B200_KEEP_NATIVE");
+    const int mode = (env && *env) ? atoi(env) : -1;
+    if (mode == 0 || pos_bytes != 1 || nseg == 0 || mat->nnz == 0) return SBLAS_B200_OK;
+    int32_t h_max = 0;
+    SB_CUDA(cudaMemcpy(&h_max, sc.hist_max, 4, cudaMemcpyDeviceToHost));
+    if (mode != 1) return SBLAS_B200_OK;
+    NativeFormat &nf = mat->native;
+    nf.nseg = nseg;
+    nf.npanels = np;
+    nf.nslots = (mat->n + kPanelWidth - 1) / kPanelWidth;
+    nf.max_col_count = h_max;
+    std::vector<int32_t> slot_panel((size_t)nf.nslots, -1);
+    for (int p = 0; p < np; ++p) slot_panel[(size_t)(panel_col_off[p] >> kPanelShift)] = p;
+    SB_CUDA(cudaMalloc((void **)&nf.d_slot_panel, (size_t)nf.nslots * 4));
+    SB_CUDA(cudaMemcpy(nf.d_slot_panel, slot_panel.data(), (size_t)nf.nslots * 4, cudaMemcpyHostToDevice));
+    nf.d_pos = sc.pos; sc.pos = nullptr;
+    nf.d_code = sc.code; sc.code = nullptr;
+    nf.d_seg_begin = sc.seg_begin; sc.seg_begin = nullptr;
+    nf.d_seg_end = sc.seg_end; sc.seg_end = nullptr;
+    nf.d_seg_pos0 = sc.seg_pos0; sc.seg_pos0 = nullptr;
+    nf.d_panel_seg_first = sc.panel_seg_first; sc.panel_seg_first = nullptr;
+    nf.state = 1;
+    mat->format_bytes += 2 * mat->entries + (int64_t)nseg * 12 + (int64_t)(np + 1 + nf.nslots) * 4;
+    return SBLAS_B200_OK;
+}
+
 static int upload_stream_impl(const void *pos_index, int pos_bytes, const uint8_t *val_index, int64_t entries,
                               const float *val_table, int32_t T, const int32_t *block_bounds,
                               const int32_t *block_index_bounds, int32_t nblocks, int32_t rows, int32_t cols,
@@ -521,8 +566,13 @@ static int upload_stream_impl(const void *pos_index, int pos_bytes, const uint8_
     SB_CUDA(cudaMalloc((void **)&sc.fillers, 16));
     SB_CUDA(cudaMemset(sc.fillers, 0, 16));
     if (nseg) {
-        SB_CUDA(cudaMalloc((void **)&sc.pos, (size_t)mat->entries * pos_bytes));
-        SB_CUDA(cudaMalloc((void **)&sc.code, (size_t)mat->entries));
+        // (+32 bytes, zeroed: the native-stream kernel reads whole 8-byte words around a segment's last entries)
+        SB_CUDA(cudaMalloc((void **)&sc.pos, (size_t)mat->entries * pos_bytes + 32));
+        SB_CUDA(cudaMalloc((void **)&sc.code, (size_t)mat->entries + 32));
+        SB_CUDA(cudaMemset(sc.pos + (size_t)mat->entries * pos_bytes, 0, 32));
+        SB_CUDA(cudaMemset(sc.code + (size_t)mat->entries, 0, 32));
+        SB_CUDA(cudaMalloc((void **)&sc.hist_max, 4));
+        SB_CUDA(cudaMemset(sc.hist_max, 0, 4));
         SB_CUDA(cudaMemcpy(sc.pos, static_cast<const uint8_t *>(pos_index) + e_begin * pos_bytes, (size_t)mat->entries * pos_bytes,
                            cudaMemcpyDefault));                  // host streams, or the device-resident ones of copyform.cu
         SB_CUDA(cudaMemcpy(sc.code, val_index + e_begin, (size_t)mat->entries, cudaMemcpyDefault));
@@ -548,6 +598,7 @@ static int upload_stream_impl(const void *pos_index, int pos_bytes, const uint8_
                                       sc.seg_panel, sc.panel_col_off, sc.seg_pos0, nseg, n, mat->k, sc.seg_hist, sc.fillers);
         else SB_LAUNCH(seg_count_kernel<uint8_t>, seg_grid, 32 * kWarpsPerCta, 0, 0, sc.pos, sc.code, T, sc.seg_begin, sc.seg_end,
                        sc.seg_panel, sc.panel_col_off, sc.seg_pos0, nseg, n, mat->k, sc.seg_hist, sc.fillers);
+        SB_LAUNCH(seg_hist_max_kernel, 148 * 4, 256, 0, 0, sc.seg_hist, (size_t)nseg * kPanelWidth, sc.hist_max);
         SB_LAUNCH(panel_bin_scan_kernel, np, kPanelWidth, 0, 0, sc.panel_seg_first, sc.panel_col_off, sc.seg_hist,
                   sc.row_len, n);
         SB_CHECK_LAUNCH();
@@ -591,7 +642,9 @@ static int upload_stream_impl(const void *pos_index, int pos_bytes, const uint8_
         SB_CHECK_LAUNCH();
     }
     SB_CUDA(cudaDeviceSynchronize());
-    return plan_spmv(mat, h_row_ptr.data());
+    rc = plan_spmv(mat, h_row_ptr.data());
+    if (rc != SBLAS_B200_OK) return rc;
+    return keep_native_streams(mat, sc, nseg, np, pos_bytes, panel_col_off);
 }
 
 static int check_stream_args(const void *pos_index, const uint8_t *val_index, int64_t entries, const float *val_table,

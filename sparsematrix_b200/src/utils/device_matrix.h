@@ -92,6 +92,24 @@ struct BlockedFormat {
     float *d_prod = nullptr;            // [total] products, written by pass 1 and read by pass 2 of the same call
 };
 
+// The reference's own streams kept on the device ("native-stream kernels"): pos_index_ / val_index_ of the
+// slab, byte for byte as CopyForm wrote them (sparse-matrix.cc:21-99), plus what the upload computes anyway -- segments of
+// 2048 stream entries that never cross a panel, and the linear position each segment starts from (the running sum of the
+// deltas before it).  src/sparse/spmv_native.cu multiplies straight from them: 2 bytes per stream entry.
+struct NativeFormat {
+    int state = 0;                      // 0 = not kept, 1 = kept
+    uint8_t *d_pos = nullptr;           // [entries + pad] one-byte position deltas
+    uint8_t *d_code = nullptr;          // [entries + pad] codebook indices (>= T: filler)
+    int32_t *d_seg_begin = nullptr;     // [nseg] first / one past the last stream entry of a segment
+    int32_t *d_seg_end = nullptr;
+    uint32_t *d_seg_pos0 = nullptr;     // [nseg] linear position (row * 256 + column in panel) before the segment's first entry
+    int32_t *d_panel_seg_first = nullptr;   // [npanels + 1] first segment of a recorded panel
+    int32_t *d_slot_panel = nullptr;    // [nslots] recorded panel of the 256 columns starting at 256 * slot, or -1
+    float *d_partial = nullptr;         // [nseg][256] column sums of a segment, written and read by one product
+    int nseg = 0, npanels = 0, nslots = 0;
+    int max_col_count = 0;              // most entries of one column inside one segment
+};
+
 struct sblas_b200_matrix {
     int device = 0;
     int32_t k = 0;           // rows of S  = length of an X row index space
@@ -161,6 +179,7 @@ struct sblas_b200_matrix {
     int dense_state = 0;                // 0 = not built yet, 1 = built, -1 = not possible (memory)
 
     BlockedFormat blocked;
+    NativeFormat native;
 
     // Tensor-core SpMM (src/sparse/spmm_tc.cu): workspace [flag | tile counters | X_hi | X_lo | split-k partial tiles]
     bool table_finite = true;           // every codebook entry is finite (else the matrix stays off that path)
@@ -205,6 +224,8 @@ constexpr int kBlockedMaxRows = 1792;   // rows per sub-block at most: 16 warps 
 int build_blocked_format(sblas_b200_matrix *mat);
 // src/sparse/spmv_blocked.cu: the rows up to long_threshold; the caller adds the long rows afterwards (beta already applied)
 int run_spmv_blocked(sblas_b200_matrix *mat, const float *x, float *y, float alpha, float beta, bool red, cudaStream_t stream);
+// src/sparse/spmv_native.cu: 0 = done, 1 = not applicable / not chosen (use the other kernels), < 0 = error
+int run_spmv_native(sblas_b200_matrix *mat, const float *x, float *y, float alpha, float beta, cudaStream_t stream);
 // records the dominant kernel of the running product: name, bytes of the device format per non-zero, and the bytes per
 // launch that do not scale with nnz besides X and C (row pointers, segment pointers, ...)
 void note_product(sblas_b200_matrix *mat, const char *kernel, int m, double bytes_per_nnz, int64_t index_bytes);

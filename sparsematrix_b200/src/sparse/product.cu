@@ -372,6 +372,34 @@ static int run_spmv(sblas_b200_matrix *mat, const float *x, float *y, float alph
     if (!staged && mat->d_row_order && is_peer_pointer(y)) return run_spmv_sorted_to_peer(mat, x, y, alpha, beta, stream);
     const int xcg = x_load_mode(mat);
     const bool red = beta == 1.0f && is_peer_pointer(y);    // y across NVLink: add at the owner, do not read it
+    // Long rows: their segment sums only read x, so they are formed on a side stream beside the kernel(s) of the other rows
+    // (config 4: 25 us of 437 when they ran behind them) and joined before the finish kernel adds them into y.
+    // SBLAS_B200_LONG_OVERLAP=0 keeps everything on one stream.
+    bool forked = false;
+    if (mat->n_long) {
+        int rc = ensure_buffer(&mat->d_partial, &mat->partial_bytes, (size_t)mat->n_long_seg * 4);
+        if (rc != SBLAS_B200_OK) return rc;
+        static const bool overlap = [] { const char *e = getenv("SBLAS_B200_LONG_OVERLAP"); return !(e && *e == '0'); }();
+        cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing(stream, &cap) != cudaSuccess) { cudaGetLastError(); cap = cudaStreamCaptureStatusNone; }
+        if (overlap && !mat->side_stream && cap == cudaStreamCaptureStatusNone) {     // nothing is created inside a capture
+            if (cudaStreamCreateWithFlags(&mat->side_stream, cudaStreamNonBlocking) != cudaSuccess ||
+                cudaEventCreateWithFlags(&mat->side_fork, cudaEventDisableTiming) != cudaSuccess ||
+                cudaEventCreateWithFlags(&mat->side_join, cudaEventDisableTiming) != cudaSuccess) {
+                cudaGetLastError();
+                if (mat->side_stream) { cudaStreamDestroy(mat->side_stream); mat->side_stream = nullptr; }
+            }
+        }
+        if (overlap && mat->side_stream && mat->side_fork && mat->side_join && !mat->profiling) {
+            SB_CUDA(cudaEventRecord(mat->side_fork, stream));
+            SB_CUDA(cudaStreamWaitEvent(mat->side_stream, mat->side_fork, 0));
+            SB_LAUNCH(spmv_long_segment_kernel, mat->n_long_seg, 256, 0, mat->side_stream, mat->d_seg_begin, mat->d_seg_end,
+                      reinterpret_cast<const int4 *>(mat->d_col), reinterpret_cast<const uint32_t *>(mat->d_code),
+                      mat->d_table, mat->T, x, alpha, mat->d_partial, xcg);
+            SB_CUDA(cudaEventRecord(mat->side_join, mat->side_stream));
+            forked = true;
+        }
+    }
     // huge x, scattered columns: the column-blocked copy in two streaming passes (spmv_blocked.cu); it applies beta to
     // every row, so the long rows below only add their sums
     const bool blocked = !staged && mat->blocked.state == 1;
@@ -397,11 +425,11 @@ static int run_spmv(sblas_b200_matrix *mat, const float *x, float *y, float alph
     }
     SB_CHECK_LAUNCH();
     if (mat->n_long) {
-        int rc = ensure_buffer(&mat->d_partial, &mat->partial_bytes, (size_t)mat->n_long_seg * 4);
-        if (rc != SBLAS_B200_OK) return rc;
-        SB_LAUNCH(spmv_long_segment_kernel, mat->n_long_seg, 256, 0, stream, mat->d_seg_begin, mat->d_seg_end,
-                  reinterpret_cast<const int4 *>(mat->d_col), reinterpret_cast<const uint32_t *>(mat->d_code),
-                  mat->d_table, mat->T, x, alpha, mat->d_partial, xcg);
+        if (forked) SB_CUDA(cudaStreamWaitEvent(stream, mat->side_join, 0));
+        else
+            SB_LAUNCH(spmv_long_segment_kernel, mat->n_long_seg, 256, 0, stream, mat->d_seg_begin, mat->d_seg_end,
+                      reinterpret_cast<const int4 *>(mat->d_col), reinterpret_cast<const uint32_t *>(mat->d_code),
+                      mat->d_table, mat->T, x, alpha, mat->d_partial, xcg);
         SB_LAUNCH(spmv_long_finish_kernel, (mat->n_long + 127) / 128, 128, 0, stream, mat->d_long_rows,
                   mat->d_long_seg_ptr, mat->d_partial, y, beta, mat->n_long, red ? 1 : 0);
         SB_CHECK_LAUNCH();

@@ -461,6 +461,9 @@ static void release(sblas_b200_matrix *mat) {
     if (mat->ws_event) cudaEventDestroy(mat->ws_event);
     if (mat->stream2) cudaStreamDestroy(mat->stream2);
     if (mat->stream3) cudaStreamDestroy(mat->stream3);
+    if (mat->side_stream) cudaStreamDestroy(mat->side_stream);
+    if (mat->side_fork) cudaEventDestroy(mat->side_fork);
+    if (mat->side_join) cudaEventDestroy(mat->side_join);
     for (cudaEvent_t ev : mat->host_events) cudaEventDestroy(ev);
     delete mat;
 }

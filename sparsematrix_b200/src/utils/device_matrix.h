@@ -164,6 +164,9 @@ struct sblas_b200_matrix {
     float *d_peer_y = nullptr;  size_t peer_y_bytes = 0;   bool peer_y_clean = false;
     // and, for large m, in slices of A/C rows so that copies in, products and copies out overlap
     cudaStream_t stream2 = nullptr, stream3 = nullptr;  // copies in / copies out
+    // SpMV with long rows: their segment sums are formed on a side stream beside the kernel of the other rows
+    cudaStream_t side_stream = nullptr;
+    cudaEvent_t side_fork = nullptr, side_join = nullptr;
     std::vector<cudaEvent_t> host_events;                // per slice: A arrived, C arrived, result ready
     int64_t format_bytes = 0;
 

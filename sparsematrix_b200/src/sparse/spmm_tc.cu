@@ -635,25 +635,6 @@ tc_fallback_kernel(const uint32_t *__restrict__ flag, uint32_t call_id, const in
     }
 }
 
-// Programmatic dependent launch: the kernel may be set up while the one before it in the stream drains; it reads what
-// that kernel wrote only after its own griddepcontrol.wait.
-template <typename... KArgs, typename... Args>
-cudaError_t launch_dependent(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args... args) {
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = grid;
-    cfg.blockDim = block;
-    cfg.dynamicSmemBytes = smem;
-    cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    const cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
-    g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
-    return e;
-}
-
 #ifdef EXP_TC_TIMELINE
 static int g_tcl_ctas = 0;
 static void dump_tc_timeline() {

@@ -39,9 +39,16 @@ spmv_blocked_pass1_kernel(const uint2 *__restrict__ lcol4, const uint32_t *__res
     float *tab_s = smem;                                    // [256][32]: entry c of lane l at c * 32 + l
     float *x_s = smem + 256 * 32;                           // [cbw]
     const int lane = threadIdx.x & 31;
-    for (int i = threadIdx.x; i < 256 * 32; i += kP1Threads) {
-        const int c = i >> 5;
-        tab_s[i] = c < T ? table[c] * alpha : 0.0f;         // val_table[code] * alpha (kernel.cc:791)
+    {
+        // one global load per thread, eight of the 32 copies of its entry each (a loop over the 8192 words was eight
+        // dependent loads per thread at the head of the kernel)
+        static_assert(kP1Threads == 1024, "four threads per codebook entry");
+        const int c = threadIdx.x >> 2;
+        const float v = c < T ? __ldg(table + c) * alpha : 0.0f;    // val_table[code] * alpha (kernel.cc:791)
+        const float4 q = make_float4(v, v, v, v);
+        float4 *dst = reinterpret_cast<float4 *>(tab_s + c * 32 + (threadIdx.x & 3) * 8);
+        dst[0] = q;
+        dst[1] = q;
     }
     // this launch covers the column blocks [cb_lo, cb_hi): quads [q_lo, q_hi), a contiguous share per CTA
     const int q_lo = cb_start[cb_lo] >> 2, total_q = (cb_start[cb_hi] >> 2) - q_lo;
@@ -264,6 +271,7 @@ int run_spmv_blocked(sblas_b200_matrix *mat, const float *x, float *y, float alp
         SB_LAUNCH(spmv_blocked_pass1_kernel<4>, grid1, kP1Threads, smem1, stream, reinterpret_cast<const uint2 *>(bf.d_lcol),
                   reinterpret_cast<const uint32_t *>(bf.d_code), bf.d_cb_start, 0, bf.ncb, bf.cbw, x, mat->k, mat->d_table, mat->T,
                   alpha, reinterpret_cast<float4 *>(bf.d_prod), x_vec);
+    // (pass 2 launched programmatically dependent on pass 1 was measured: the cold step went from 410 to 446 us, r02)
 #define SB_P2(DD) SB_LAUNCH(spmv_blocked_pass2_kernel<DD>, grid2, 32 * kP2Warps, smem2, stream, reinterpret_cast<const uint2 *>(bf.d_lrow), \
               reinterpret_cast<const float4 *>(bf.d_prod), bf.d_seg_ptr, 0, bf.ncb, bf.nsub, bf.rs, mat->n, y, beta, red ? 1 : 0, abl)
     if (only != 1) {

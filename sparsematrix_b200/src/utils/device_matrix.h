@@ -238,6 +238,26 @@ void forget_host_buffers(const void *owner, const void *ptr);      // ptr != nul
 // src/sparse/product.cu
 int product_on_stream(sblas_b200_matrix *mat, const float *d_a, int32_t m, int32_t lda, float *d_c, int32_t ldc,
                       float alpha, float beta, cudaStream_t stream);
+// Programmatic dependent launch: the kernel may be set up while the one before it in the stream drains; it reads what
+// that kernel wrote only after its own griddepcontrol.wait.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_dependent(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+    g_kernel_launches.fetch_add(1, std::memory_order_relaxed);
+    return e;
+}
+
+
 }  // namespace sblas_b200
 
 #endif

@@ -2,7 +2,7 @@
 # One gpurun call: GPU parity tests, the C++ harness, bench lines for every config, the reference arm,
 # and an ncu launch list of the default bench (full captures: tools/gpu_ncu.sh, one per gpurun call).
 # Usage (from the repo root, under gpurun):  bash tools/gpu_round.sh [tag]
-TAG=${1:-r01}
+TAG=${1:-r02}
 OUT=gpurun_out/$TAG
 mkdir -p $OUT
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $OUT/gpu.txt 2>&1

@@ -767,7 +767,11 @@ int run_spmm_tc(sblas_b200_matrix *mat, const float *d_a, int m, int lda, float 
     if (need > mat->tc_ws_bytes || head_pad != mat->tc_head_bytes) {
         if (capturing) return 1;                                // no allocation (or re-initialisation) inside a capture
         const int rc = ensure_buffer(&mat->d_tc_ws, &mat->tc_ws_bytes, need);
-        if (rc != SBLAS_B200_OK) return rc;
+        if (rc != SBLAS_B200_OK) {                              // no room for the operand images (2 x the size of A, padded, and
+            cudaGetLastError();                                 // the partial tiles): the CUDA-core kernels run this product
+            mat->tc_head_bytes = 0;
+            return 1;
+        }
         SB_CUDA(cudaMemsetAsync(mat->d_tc_ws, 0, head_pad, stream));   // flag 0 (call ids start at 1), counters 0
         mat->tc_head_bytes = head_pad;
     }

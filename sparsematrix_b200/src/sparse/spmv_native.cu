@@ -169,7 +169,11 @@ int run_spmv_native(sblas_b200_matrix *mat, const float *x, float *y, float alph
         if (cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone; cudaStreamIsCapturing(stream, &cap) == cudaSuccess && cap != cudaStreamCaptureStatusNone)
             return 1;                                           // no allocation inside a capture
         cudaGetLastError();
-        SB_CUDA(cudaMalloc((void **)&nf.d_partial, (size_t)nf.nseg * 256 * 4));
+        if (cudaMalloc((void **)&nf.d_partial, (size_t)nf.nseg * 256 * 4) != cudaSuccess) {   // no room: the other kernels
+            cudaGetLastError();
+            nf.d_partial = nullptr;
+            return 1;
+        }
     }
     struct Timer {                                              // event pair around both kernels when profiling
         sblas_b200_matrix *mat; cudaStream_t st; cudaEvent_t a = nullptr, b = nullptr;

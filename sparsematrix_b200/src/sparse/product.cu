@@ -708,7 +708,20 @@ static int host_product_overlapped(sblas_b200_matrix *mat, const float *a, int m
                                    int ldc, float alpha, float beta) {
     const int n = mat->n, k = mat->k;
     const size_t elems = (size_t)m * n, padded = (elems + 3) & ~(size_t)3;
-    const std::vector<int> bounds = host_slice_bounds(mat, m);
+    // m == 1 with a long y (config 4: 32 MB each way): there are no rows of A / C to slice, so y is cut into column ranges
+    // instead -- x travels in, then the ranges of y; ONE product; then range after range is combined and copied out while
+    // the later ranges are still travelling in.  SBLAS_B200_HOST_COLSLICE=0 keeps the single direct pass.
+    static const bool colslice_on = [] { const char *e = getenv("SBLAS_B200_HOST_COLSLICE"); return !(e && *e == '0'); }();
+    const bool colmode = colslice_on && m == 1 && (size_t)n * 4 >= ((size_t)8 << 20);
+    std::vector<int> bounds;
+    if (colmode) {
+        const int parts = (int)std::min<size_t>(8, (size_t)n * 4 / ((size_t)4 << 20));
+        bounds.push_back(0);
+        for (int q = 1; q < parts; ++q) bounds.push_back((int)(((int64_t)n * q / parts) & ~(int64_t)1023));
+        bounds.push_back(n);
+    } else {
+        bounds = host_slice_bounds(mat, m);
+    }
     const int slices = (int)bounds.size() - 1;
     if (!mat->stream2) SB_CUDA(cudaStreamCreateWithFlags(&mat->stream2, cudaStreamNonBlocking));
     if (!mat->stream3) SB_CUDA(cudaStreamCreateWithFlags(&mat->stream3, cudaStreamNonBlocking));
@@ -742,6 +755,19 @@ static int host_product_overlapped(sblas_b200_matrix *mat, const float *a, int m
     auto fail_sync = [&](int code) { cudaStreamSynchronize(mat->stream2); cudaStreamSynchronize(mat->stream3);
                                      cudaStreamSynchronize(mat->stream); return code; };
     auto copy_in = [&](bool is_a, int s) -> cudaError_t {
+        if (colmode) {                                  // x once, then y columns [bounds[s], bounds[s + 1])
+            cudaError_t ce = cudaSuccess;
+            if (is_a) {
+                if (s != 0) return cudaSuccess;
+                ce = cudaMemcpyAsync(mat->d_host_a, a, (size_t)k * 4, cudaMemcpyHostToDevice, mat->stream2);
+            } else {
+                ce = cudaMemcpyAsync(mat->d_host_c + bounds[s], c + bounds[s], (size_t)(bounds[s + 1] - bounds[s]) * 4,
+                                     cudaMemcpyHostToDevice, mat->stream2);
+            }
+            if (ce == cudaSuccess) ce = cudaEventRecord(mat->host_events[3 * s + (is_a ? 0 : 1)], mat->stream2);
+            mark(is_a ? "x in" : "y range in", mat->stream2);
+            return ce;
+        }
         const int i0 = bounds[s], mi = bounds[s + 1] - i0;
         cudaError_t e = is_a
             ? copy_rows(mat->d_host_a + (size_t)i0 * k, (size_t)k * 4, a + (size_t)i0 * lda, (size_t)lda * 4,
@@ -761,7 +787,32 @@ static int host_product_overlapped(sblas_b200_matrix *mat, const float *a, int m
     if (e != cudaSuccess) return fail_sync(cuda_fail(e, "host path copies in", __FILE__, __LINE__));
     const bool direct = slices == 1;                    // one slice: the combine kernel writes the caller's C itself
     // (every slice written through the mapped pointer instead of copied out: 2160-2740 us on config 3 against 1700, r02)
-    for (int s = 0; s < slices; ++s) {
+    for (int s = 0; colmode && s < slices; ++s) {
+        const int j0 = bounds[s], w = bounds[s + 1] - j0;
+        if (s == 0) {
+            e = cudaStreamWaitEvent(mat->stream, mat->host_events[0], 0);
+            if (e != cudaSuccess) return fail_sync(cuda_fail(e, "host path wait x", __FILE__, __LINE__));
+            rc = product_on_stream(mat, mat->d_host_a, 1, k, mat->d_host_p, n, alpha, 1.0f, mat->stream);
+            if (rc != SBLAS_B200_OK) return fail_sync(rc);
+            mark("product done", mat->stream);
+        }
+        e = cudaStreamWaitEvent(mat->stream, mat->host_events[3 * s + 1], 0);
+        if (e != cudaSuccess) return fail_sync(cuda_fail(e, "host path wait y range", __FILE__, __LINE__));
+        float *p = mat->d_host_p + j0, *cs = mat->d_host_c + j0;
+        const bool vec = (w & 3) == 0 && (j0 & 3) == 0;
+        const size_t work = vec ? (size_t)w / 4 : (size_t)w;
+        const unsigned grid = (unsigned)std::min<size_t>((work + 255) / 256, 148 * 16);
+        if (vec) SB_LAUNCH(combine_out_kernel<true>, grid, 256, 0, mat->stream, cs, p, mat->d_row_ptr + j0, cs, w, 1, w, beta);
+        else SB_LAUNCH(combine_out_kernel<false>, grid, 256, 0, mat->stream, cs, p, mat->d_row_ptr + j0, cs, w, 1, w, beta);
+        e = cudaGetLastError();
+        mark("combine done", mat->stream);
+        if (e == cudaSuccess) e = cudaEventRecord(mat->host_events[3 * s + 2], mat->stream);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(mat->stream3, mat->host_events[3 * s + 2], 0);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(c + j0, cs, (size_t)w * 4, cudaMemcpyDeviceToHost, mat->stream3);
+        mark("y range out", mat->stream3);
+        if (e != cudaSuccess) return fail_sync(cuda_fail(e, "host path combine / copy out", __FILE__, __LINE__));
+    }
+    for (int s = 0; !colmode && s < slices; ++s) {
         const int i0 = bounds[s], mi = bounds[s + 1] - i0;
         float *p = mat->d_host_p + (size_t)i0 * n, *cs = mat->d_host_c + (size_t)i0 * n;
         e = cudaStreamWaitEvent(mat->stream, mat->host_events[3 * s], 0);

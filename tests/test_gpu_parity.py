@@ -1068,3 +1068,24 @@ def test_blocked_spmv_is_built_only_on_request_for_small_matrices():
     dev = sb.DeviceMatrix.upload_csr(row_ptr, col, code, tab, 255, n, k)
     dev.addmatmat_host(a, 1, k, np.zeros((1, n), np.float32), n, 1.0, 1.0)
     assert dev.last_product()["kernel"].startswith("spmv_rows")              # small: the row kernels stay
+
+
+def test_host_entry_point_cuts_a_long_y_into_column_ranges():
+    """m = 1 with y of 8 MB or more and caller buffers from sblas_b200_host_alloc: x in, the column ranges of y in, ONE product,
+    then range after range combined and copied out (product.cu: host_product_overlapped, colmode).  Same kernels as from
+    pageable buffers, so the same bits; columns of S without entries keep their (scaled) value bit for bit."""
+    n, k = (5 << 19) + 37, 4096                                 # 10 MB of y, not a multiple of the range alignment
+    row_ptr, col, code = gen.powerlaw_csr(n, k, seed=23, x_min=2, cap=64)
+    lens = np.diff(row_ptr)
+    tab = gen.codebook()
+    dev = sb.DeviceMatrix.upload_csr(row_ptr, col, code, tab, 255, n, k)
+    a = gen.dense_uniform((1, k), 2); c0 = gen.dense_uniform((1, n), 3)
+    empty = np.flatnonzero(lens == 0)[:8]
+    if empty.size: c0[0, empty[0]] = -0.0
+    for alpha, beta in ((1.0, 1.0), (1.3, 2.0), (0.7, 0.0)):
+        want = dev.addmatmat_host(a, 1, k, c0.copy(), n, alpha, beta)              # numpy (pageable) buffers
+        h_a = sb.host_buffer((1, k)); h_a[...] = a
+        h_c = sb.host_buffer((1, n)); h_c[...] = c0
+        got = dev.addmatmat_host(h_a, 1, k, h_c, n, alpha, beta)
+        assert_bits_equal(np.asarray(got).reshape(-1), want.reshape(-1), f"column ranges vs one pass, alpha={alpha} beta={beta}")
+    dev.free()

@@ -1089,3 +1089,32 @@ def test_host_entry_point_cuts_a_long_y_into_column_ranges():
         got = dev.addmatmat_host(h_a, 1, k, h_c, n, alpha, beta)
         assert_bits_equal(np.asarray(got).reshape(-1), want.reshape(-1), f"column ranges vs one pass, alpha={alpha} beta={beta}")
     dev.free()
+
+
+def test_spmv_with_long_rows_can_be_captured_into_a_cuda_graph():
+    # the long rows' segment sums run on a side stream of the handle (forked from and joined back into the caller's stream):
+    # inside a capture that fork and join become graph edges; replays give the eager bits
+    import torch
+    n, k = 70000, 30000
+    row_ptr, col, code = gen.powerlaw_csr(n, k, seed=31, x_min=4, cap=20000)
+    dev = sb.DeviceMatrix.upload_csr(row_ptr, col, code, gen.codebook(), 255, n, k)
+    assert dev.info().long_rows > 0, "the case needs rows on the split-row path"
+    cuda = torch.device("cuda", 0)
+    x = torch.from_numpy(gen.dense_uniform((1, k), 5)).to(cuda)
+    y0 = torch.from_numpy(gen.dense_uniform((1, n), 6)).to(cuda)
+    y = y0.clone()
+    dev.addmatmat_dev(x, 1, k, y, n, 1.3, 0.7)                  # eager: warm-up (side stream, workspaces) and the expected bits
+    torch.cuda.synchronize()
+    want = y.cpu().numpy()
+    yg = y0.clone()
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph, stream=side):
+        dev.addmatmat_dev(x, 1, k, yg, n, 1.3, 0.7, stream=side.cuda_stream)
+    for rep in range(2):
+        yg.copy_(y0)
+        graph.replay()
+        torch.cuda.synchronize()
+        assert_bits_equal(yg.cpu().numpy(), want, f"replay {rep}")
+    dev.free()
